@@ -1,0 +1,225 @@
+"""Seeded generator of synthetic inputs in the reference's on-disk formats.
+
+Formats follow the reference's serialisers / parsers:
+  * model directory ........ src/BuildModel.java:1135-1197 (serializeStatistics) / :1200-1282 (parser)
+  * repeatIntervals.txt .... src/BuildModel.java:464-480   ("count", then "type,start,end")
+  * segdups.txt ............ src/BuildModel.java:581-598   ("count", then "start,end")
+  * insertion strings ...... src/SimulateHaplotypes.java:313-337 (one string per line, sorted by length)
+  * reference FASTA ........ src/SimulateHaplotypes.java:119-134 (one header line, then sequence lines)
+  * length-bin files ....... src/BuildReadLengthBins.java:42-105 ("<prefix><i>.bin", 4-line FASTQ records)
+  * pbsim2 HMM model ....... docker/pbsim2.cpp:2583-2647 ("<acc> IP|EP|TP <state> <probs...>")
+
+Everything is a pure function of (shape parameters, seed); numpy only.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+GENERATOR_SEED = 20261104
+SV_TYPES = ("DEL", "DUP", "INS", "INV")
+AF_NAMES = ("ALL", "AFR", "AMR", "EAS", "EUR", "OTH")
+N_LENGTH_BINS = 1 + (1000000 - 50 + 1) // 50  # src/BuildModel.java:919
+AF_NBINS = 10000
+
+GRCH38_LENGTHS = {
+    "chr1": 248956422, "chr2": 242193529, "chr3": 198295559, "chr4": 190214555, "chr5": 181538259,
+    "chr6": 170805979, "chr7": 159345973, "chr8": 145138636, "chr9": 138394717, "chr10": 133797422,
+    "chr11": 135086622, "chr12": 133275309, "chr13": 114364328, "chr14": 107043718, "chr15": 101991189,
+    "chr16": 90338345, "chr17": 83257441, "chr18": 80373285, "chr19": 58617616, "chr20": 64444167,
+    "chr21": 46709983, "chr22": 50818468, "chrX": 156040895, "chrY": 57227415,
+}
+
+
+@dataclass
+class SynthInputs:
+    root: str
+    reference_file: str
+    model_dir: str
+    repeat_intervals_file: str
+    segdups_file: str
+    insertions_file: str
+    n_insertions: int
+    reference_length: int
+    extra: dict = field(default_factory=dict)
+
+    def simulate_argv(self, out_dir: str, n_individuals: int, n_frequent: int = 5000,
+                      af_threshold: str = "0.01", population: str = "ALL") -> list[str]:
+        """Positional argv of SimulateHaplotypes (src/SimulateHaplotypes.java:76-86)."""
+        return [self.model_dir, population, self.reference_file, self.repeat_intervals_file, self.segdups_file,
+                self.insertions_file, str(self.n_insertions), af_threshold, str(n_frequent), str(n_individuals),
+                out_dir]
+
+
+def random_reference(length: int, seed: int = GENERATOR_SEED):
+    """uint8[length] of i.i.d. ACGT with N runs at both ends and a centromere block, plus interval tables.
+
+    Returns (bases, repeat_intervals[int32 n x 3: type,start,end], segdups[int32 m x 2]).
+    """
+    rng = np.random.default_rng(seed)
+    bases = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=length, dtype=np.uint8)].copy()
+    end_n = min(10000, max(1, length // 100))
+    bases[:end_n] = ord("N")
+    bases[length - end_n:] = ord("N")
+    c0 = int(0.49 * length)
+    c1 = min(length - end_n, c0 + int(0.07 * length))
+    bases[c0:c1] = ord("N")
+
+    # repeat intervals: alternating gap / interval lengths ~ Geometric(mean 300)
+    n_est = int(length / 600 * 1.3) + 16
+    gaps = rng.geometric(1.0 / 300.0, size=n_est).astype(np.int64) + 30
+    lens = rng.geometric(1.0 / 300.0, size=n_est).astype(np.int64)
+    starts = np.cumsum(gaps + np.concatenate(([0], lens[:-1]))) + end_n
+    ends = starts + lens - 1
+    keep = ends < length - end_n - 1
+    starts, ends = starts[keep], ends[keep]
+    types = rng.choice(3, size=starts.size, p=[0.85, 0.10, 0.05]).astype(np.int64)
+    repeat_intervals = np.stack([types, starts, ends], axis=1).astype(np.int32)
+
+    # soft-mask (lower-case) exactly on repeat intervals
+    delta = np.zeros(length + 1, dtype=np.int32)
+    np.add.at(delta, starts, 1)
+    np.add.at(delta, ends + 1, -1)
+    mask = np.cumsum(delta[:-1]) > 0
+    mask &= bases != ord("N")
+    bases[mask] |= 0x20
+
+    # segdups: ~5 % of the sequence, lengths log-uniform in [1 kbp, 100 kbp] (scaled down for tiny references)
+    hi = min(100000.0, max(2000.0, length / 50))
+    target = int(0.05 * length)
+    seg = []
+    total = 0
+    while total < target:
+        ln = int(np.exp(rng.uniform(np.log(1000.0), np.log(hi))))
+        st = int(rng.integers(end_n, max(end_n + 1, length - end_n - ln - 1)))
+        seg.append((st, st + ln - 1))
+        total += ln
+    seg.sort()
+    merged = []
+    for s, e in seg:
+        if merged and s - merged[-1][1] < 25:
+            merged[-1] = (merged[-1][0], max(merged[-1][1], e))
+        else:
+            merged.append((s, e))
+    segdups = np.array(merged, dtype=np.int32).reshape(-1, 2)
+    return bases, repeat_intervals, segdups
+
+
+def write_fasta(path: str, header: str, bases: np.ndarray, width: int = 60) -> None:
+    n = bases.size
+    full = n // width
+    with open(path, "wb") as f:
+        f.write(b">" + header.encode() + b"\n")
+        if full:
+            block = np.empty((full, width + 1), dtype=np.uint8)
+            block[:, :width] = bases[: full * width].reshape(full, width)
+            block[:, width] = ord("\n")
+            f.write(block.tobytes())
+        if n % width:
+            f.write(bases[full * width:].tobytes() + b"\n")
+
+
+def _cum_row(weights: np.ndarray) -> np.ndarray:
+    c = np.cumsum(weights.astype(np.float64))
+    c /= c[-1]
+    c[-1] = 1.0
+    nz = np.nonzero(weights)[0]
+    if nz.size:
+        c[nz[-1]:] = 1.0  # every cumulative row reaches exactly 1.0 at its last non-empty bin
+    return c
+
+
+def _fmt_row(vals) -> str:
+    return ",".join(repr(float(v)) for v in vals) + ","
+
+
+def write_model(model_dir: str, seed: int = GENERATOR_SEED, max_sv_length: int = 1000000,
+                max_ins_length: int = 10000, frac_frequent: float | None = None) -> None:
+    """BuildModel-format model directory. `max_sv_length` caps the mass of the length CDFs (tests on small
+    references); INS rows carry zero mass above `max_ins_length`."""
+    os.makedirs(model_dir, exist_ok=True)
+    rng = np.random.default_rng(seed + 1)
+    with open(os.path.join(model_dir, "statistics_svType.txt"), "w") as f:
+        f.write("4\n" + _fmt_row([0.52, 0.67, 0.998, 1.0]) + "\n")
+    with open(os.path.join(model_dir, "statistics_intervalType.txt"), "w") as f:
+        f.write("4,5\n")
+        for _ in range(4):
+            w = rng.dirichlet([2.0] * 5)
+            f.write(_fmt_row(_cum_row(w)) + "\n")
+    centers = 50.0 + 50.0 * np.arange(N_LENGTH_BINS) + 25.0
+    base = 1.0 / centers  # log-uniform density integrated over equal-width bins
+    with open(os.path.join(model_dir, "statistics_length.txt"), "w") as f:
+        f.write(f"4,5,{N_LENGTH_BINS}\n")
+        for t in range(4):
+            for _ in range(5):
+                w = base * rng.uniform(0.8, 1.2)
+                w = w + 40.0 * base.sum() / N_LENGTH_BINS * np.exp(-0.5 * ((centers - 300.0) / 60.0) ** 2)
+                w = w + 8.0 * base.sum() / N_LENGTH_BINS * np.exp(-0.5 * ((centers - 6000.0) / 300.0) ** 2)
+                cap = max_ins_length if t == 2 else max_sv_length
+                # INS: length/50 must stay below nBins = 1 + max_ins_length/50  =>  p <= max_ins_length/50 - 1
+                last_bin = (cap // 50 - 1) if t == 2 else max(0, (cap - 50 - 49) // 50)
+                w[last_bin + 1:] = 0.0
+                f.write(_fmt_row(_cum_row(w)) + "\n")
+    af_min, af_max = 4.6e-5, 1.0
+    q = (af_max - af_min) / (AF_NBINS - 1)
+    af_centers = af_min + q * (np.arange(AF_NBINS) + 0.5)
+    for name in AF_NAMES:
+        with open(os.path.join(model_dir, f"statistics_alleleFrequency_{name}.txt"), "w") as f:
+            f.write(f"4,{AF_NBINS}\n")
+            for _ in range(4):
+                w = 1.0 / af_centers  # mass ∝ 1/AF
+                if frac_frequent is not None:
+                    below = af_centers < 0.01
+                    w[below] *= (1.0 - frac_frequent) / w[below].sum()
+                    w[~below] *= frac_frequent / w[~below].sum()
+                f.write(repr(af_min) + "," + repr(af_max) + "," + _fmt_row(_cum_row(w)) + "\n")
+    with open(os.path.join(model_dir, "statistics_position.txt"), "w") as f:
+        f.write("4,10\n")
+        for _ in range(4):
+            f.write(_fmt_row(_cum_row(np.ones(10))) + "\n")
+
+
+def write_insertions(path: str, n: int, seed: int = GENERATOR_SEED, max_len: int = 10000) -> int:
+    """`n` distinct ACGT strings sorted by length (50..max_len), at least one in the top 50-bp bin."""
+    rng = np.random.default_rng(seed + 2)
+    lens = np.exp(rng.uniform(np.log(50.0), np.log(max_len), size=n)).astype(np.int64)
+    lens[: max(1, n // 200)] = max_len  # the top bin is never empty
+    lens = np.sort(np.clip(lens, 50, max_len))
+    alphabet = np.frombuffer(b"ACGT", dtype=np.uint8)
+    blob = alphabet[rng.integers(0, 4, size=int(lens.sum()), dtype=np.uint8)]
+    out = np.empty(blob.size + n, dtype=np.uint8)
+    ends = np.cumsum(lens) + np.arange(n)
+    out[:] = 0
+    out[ends] = ord("\n")
+    out[out == 0] = blob
+    with open(path, "wb") as f:
+        f.write(out.tobytes())
+    return n
+
+
+def generate_population_inputs(root: str, length: int, seed: int = GENERATOR_SEED, n_insertions: int = 30000,
+                               max_sv_length: int | None = None, frac_frequent: float | None = None) -> SynthInputs:
+    os.makedirs(root, exist_ok=True)
+    bases, rep, seg = random_reference(length, seed)
+    ref = os.path.join(root, "reference.fa")
+    write_fasta(ref, "chr1", bases)
+    repf = os.path.join(root, "repeatIntervals.txt")
+    with open(repf, "w") as f:
+        f.write(f"{rep.shape[0]}\n")
+        np.savetxt(f, rep, fmt="%d", delimiter=",")
+    segf = os.path.join(root, "segdups.txt")
+    with open(segf, "w") as f:
+        f.write(f"{seg.shape[0]}\n")
+        np.savetxt(f, seg, fmt="%d", delimiter=",")
+    if max_sv_length is None:
+        max_sv_length = min(1000000, max(100, length // 40))
+    max_ins = min(10000, max(100, (length // 100) // 50 * 50))
+    model_dir = os.path.join(root, "model")
+    write_model(model_dir, seed, max_sv_length=max_sv_length, max_ins_length=max_ins, frac_frequent=frac_frequent)
+    insf = os.path.join(root, "insertions.txt")
+    write_insertions(insf, n_insertions, seed, max_len=max_ins)
+    return SynthInputs(root=root, reference_file=ref, model_dir=model_dir, repeat_intervals_file=repf,
+                       segdups_file=segf, insertions_file=insf, n_insertions=n_insertions,
+                       reference_length=length, extra={"bases": bases, "repeat_intervals": rep, "segdups": seg})
