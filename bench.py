@@ -1,0 +1,289 @@
+#!/usr/bin/env python
+"""bench.py — haplotype materialisation throughput (simulated haplotype Gbp/s) on B200.
+
+Workload (BASELINE.json configs[1]): chr1-sized synthetic reference (248 956 422 bp), 1 000 haplotypes,
+per-haplotype SV edit lists -> segment scan -> tiled copy kernel. One "step" = one batch of `--batch` haplotypes
+(plan kernels + materialisation kernel) with all inputs resident in HBM; K steps walk through the 1 000 haplotypes.
+Inputs per step (>= 31 GB written, 249 MB reference) are far larger than the 126 MB L2, so no flush is needed.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Under torchrun each rank owns its own shard of haplotypes (individuals are sharded, no data-path collective):
+weak scaling. `--impl reference` times the CPU restatement of the reference path (oracle/, kind "port": no JVM in
+this image) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "population-sv-simulator_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+CHR1 = 248_956_422
+N_HAPLOTYPES = 1000
+ALGO_BYTES_PER_BP = 2.0  # 1 B read (reference/payload) + 1 B written per output base
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def synth_population(L: int, H: int, seed: int = 20261104):
+    """Synthetic variant table + per-haplotype edit lists of the shape SimulateHaplotypes produces
+    (V ~ 11k SVs, ~1.1k per haplotype, type mix DEL .52 / DUP .15 / INS .328 / INV .002, globally non-overlapping so
+    every subset is collision-free). Used until row G/C/S1 feed the bench from the real sampler."""
+    rng = np.random.default_rng(seed)
+    V = min(11000, max(8, L // 4000))
+    types = rng.choice(4, size=V, p=[0.52, 0.15, 0.328, 0.002]).astype(np.int8)
+    slot = (L - 2000) // V
+    maxlen = min(20000, slot // 2)
+    length = np.minimum(np.exp(rng.uniform(np.log(50), np.log(maxlen), size=V)), maxlen).astype(np.int32)
+    pos = (1000 + np.arange(V, dtype=np.int64) * slot + rng.integers(0, slot - maxlen - 1, size=V)).astype(np.int32)
+    plen = np.where(types == 2, length, 0).astype(np.int64)
+    payload_off = np.concatenate(([0], np.cumsum(plen))).astype(np.int64)
+    payload = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=int(plen.sum()), dtype=np.uint8)].copy()
+    af = np.exp(rng.uniform(np.log(4.6e-5), 0.0, size=V))
+    carr = rng.random((H, V)) < af[None, :]
+    lists = [np.nonzero(carr[h])[0].astype(np.int32) for h in range(H)]
+    list_off = np.concatenate(([0], np.cumsum([l.size for l in lists]))).astype(np.int64)
+    ids = np.concatenate(lists).astype(np.int32)
+    return dict(sv_type=types, position=pos, length=length, payload_off=payload_off, payload=payload, lists=lists,
+                list_off=list_off, ids=ids)
+
+
+def random_reference(L: int, seed: int = 20261104) -> np.ndarray:
+    rng = np.random.default_rng(seed)
+    return np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=L, dtype=np.uint8)].copy()
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index = index
+        self.rows = []
+        self.stop_flag = False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_baseline_sample(ref, pop, budget_s: float = 12.0, max_haps: int = 64):
+    """The oracle's restatement of buildHaplotypes (single thread, as the reference is) on a bounded sample."""
+    import oracle_helpers as oh
+    olib = oh.load_oracle()
+    t0 = time.perf_counter()
+    bases = 0
+    n = 0
+    for h in range(max_haps):
+        out = oh.build_haplotype(olib, ref, pop["sv_type"], pop["position"], pop["length"], pop["payload_off"],
+                                 pop["payload"], None, pop["lists"][h])
+        bases += out.size
+        n += 1
+        if time.perf_counter() - t0 > budget_s and n >= 2:
+            break
+    dt = time.perf_counter() - t0
+    return bases / dt / 1e9, n, dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--batch", type=int, default=125, help="haplotypes per step (per GPU)")
+    ap.add_argument("--length", type=int, default=CHR1)
+    ap.add_argument("--e2e-haplotypes", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    L = args.length
+    workload = f"chr1-sized reference ({L} bp), {N_HAPLOTYPES} haplotypes, materialisation in batches of {args.batch}"
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        ref = random_reference(L)
+        pop = synth_population(L, max(64, args.batch))
+        vals = []
+        per = max(1, min(8, 64 // max(1, args.steps + args.warmup)))
+        import oracle_helpers as oh
+        olib = oh.load_oracle()
+        h = 0
+        t_all = []
+        for s in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            bases = 0
+            for _ in range(per):
+                out = oh.build_haplotype(olib, ref, pop["sv_type"], pop["position"], pop["length"], pop["payload_off"],
+                                         pop["payload"], None, pop["lists"][h % len(pop["lists"])])
+                bases += out.size
+                h += 1
+            dt = time.perf_counter() - t0
+            if s >= args.warmup:
+                vals.append(bases / dt / 1e9)
+                t_all.append(dt)
+        v = float(np.mean(vals))
+        line = {"metric": "simulated haplotype Gbp/s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(t_all)), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
+                "config": {"workload": workload, "l2": "inputs larger than L2"},
+                "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": 1, "kind": "port",
+                                 "sample": f"{per} haplotypes per step (CPU restatement of buildHaplotypes, single thread; no JVM in this image)"},
+                "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    from synthpop import lib as splib
+
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    ref = random_reference(L)
+    pop = synth_population(L, N_HAPLOTYPES)
+    ctx = splib.Context(local_rank, 42)
+    stream = torch.cuda.Stream()
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_reference(ref)
+    ctx.set_variants(pop["sv_type"], pop["position"], pop["length"], pop["payload_off"], pop["payload"])
+    ctx.set_haplotype_lists(pop["list_off"], pop["ids"])
+
+    # each rank owns a contiguous shard of the 1 000 haplotypes' worth of work (weak scaling: `batch` per step per GPU)
+    nb = N_HAPLOTYPES // args.batch
+    def batch_range(step):
+        b = (step + rank * 3) % nb
+        return b * args.batch, b * args.batch + args.batch - 1
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    launches0 = 0
+    step_events = []
+    bases_total = 0
+    sampler = ClockSampler(local_rank)
+    for s in range(args.warmup + args.steps):
+        if s == args.warmup:
+            barrier()
+            sampler.start()
+            launches0 = ctx.kernel_launches
+            t_wall0 = time.perf_counter()
+        a, b = batch_range(s)
+        with torch.cuda.stream(stream):
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e2 = torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            lens, stride = ctx.plan_haplotypes(a, b, False)
+            e1.record(stream)
+            ctx.materialise()
+            e2.record(stream)
+        if s >= args.warmup:
+            step_events.append((e0, e1, e2))
+            bases_total += int(lens.sum())
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    sampler.stop_flag = True
+    launches = ctx.kernel_launches - launches0
+    t_step = sum(e0.elapsed_time(e2) for e0, e1, e2 in step_events) / 1e3
+    t_kernel = sum(e1.elapsed_time(e2) for e0, e1, e2 in step_events) / 1e3
+    t = torch.tensor([t_step, t_kernel, float(bases_total)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        t_step_max, t_kernel_max, bases_all = float(tmax[0]), float(tmax[1]), float(tsum[2])
+    else:
+        t_step_max, t_kernel_max, bases_all = t_step, t_kernel, float(bases_total)
+    value = bases_all / t_step_max / 1e9
+
+    # e2e: the reference-facing call with HOST buffers — reference + variant table + lists H2D, plan, materialise, D2H
+    ne = args.e2e_haplotypes
+    host_out = torch.empty(int((L + (4 << 20)) * ne), dtype=torch.uint8, pin_memory=True)
+    host_np = host_out.numpy()
+    ref_pinned = torch.from_numpy(ref).pin_memory().numpy()
+    e2e_t, e2e_bases, h2d, d2h = [], 0, 0, 0
+    for s in range(2 + 3):
+        barrier()
+        t0 = time.perf_counter()
+        ctx.set_reference(ref_pinned)
+        ctx.set_variants(pop["sv_type"], pop["position"], pop["length"], pop["payload_off"], pop["payload"])
+        ctx.set_haplotype_lists(pop["list_off"], pop["ids"])
+        offs = ctx.build_haplotypes_host(s * ne, s * ne + ne - 1, host_np, False)
+        barrier()
+        if s >= 2:
+            e2e_t.append(time.perf_counter() - t0)
+            e2e_bases += int(offs[-1])
+            h2d = int(ref.nbytes + pop["sv_type"].nbytes + pop["position"].nbytes + pop["length"].nbytes +
+                      pop["payload_off"].nbytes + pop["payload"].nbytes + pop["list_off"].nbytes + pop["ids"].nbytes)
+            d2h = int(offs[-1])
+    e2e_val = torch.tensor([e2e_bases / sum(e2e_t) / 1e9], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(e2e_val, op=dist.ReduceOp.SUM)
+
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        per_rank_bases = bases_total
+        achieved = ALGO_BYTES_PER_BP * per_rank_bases / t_kernel / 1e9
+        line = {"metric": "simulated haplotype Gbp/s", "value": value, "unit": "Gbp/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * t_step_max / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": workload, "haplotypes_per_step_per_gpu": args.batch,
+                           "l2": "inputs larger than L2 (>=31 GB written per step)", "sharding": "by individual, no collective"},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "kernel": "materialise_kernel", "peak_kind": peak_kind,
+                             "algorithmic_bytes_per_bp": ALGO_BYTES_PER_BP, "kernel_ms_per_step": 1e3 * t_kernel / args.steps},
+                "e2e": {"value": float(e2e_val[0]), "unit": "Gbp/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "haplotypes_per_call": ne},
+                "clocks": sampler.summary(), "wall_s_timed_region": t_wall}
+        if world == 1 and not args.no_cpu_baseline:
+            v, n, dt = cpu_baseline_sample(ref, pop)
+            line["cpu_baseline"] = {"value": v, "unit": "Gbp/s", "cores": 1, "kind": "port",
+                                    "sample": f"{n} chr1-sized haplotypes in {dt:.1f} s (CPU restatement of buildHaplotypes, 1 thread)"}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

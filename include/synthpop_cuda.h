@@ -1,0 +1,83 @@
+/*
+ * libsynthpop_cuda.so — C ABI of the B200-native population-simulation hot path.
+ *
+ * The reference (fabio-cunial/population-sv-simulator) has no FFI: its boundary is three Java CLIs with
+ * positional argv, the static methods other classes call, and on-disk formats. Every entry
+ * point below names the reference interface it replaces (file:line relative to the reference root). A Java
+ * host (JNI / Panama FFM) or the C++ CLI host in population-sv-simulator_b200/host binds exactly these.
+ *
+ * Conventions: plain pointers and sizes only; every function returns int (0 = ok, 3 = SampleReadsFromLengthBins
+ * "coverage unreachable" [src/SampleReadsFromLengthBins.java:64-67], any other non-zero = error, message via
+ * sp_last_error). The library owns all device memory inside sp_ctx; the caller owns host buffers it passes.
+ * One sp_ctx per host thread; calls are blocking unless stated. There is no CPU fallback: without a CUDA
+ * device sp_create fails.
+ */
+#ifndef SYNTHPOP_CUDA_H
+#define SYNTHPOP_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sp_ctx sp_ctx;
+
+enum { SP_OK = 0, SP_ERR = 1, SP_ERR_COVERAGE = 3, SP_ERR_CUDA = 4, SP_ERR_ARG = 5, SP_ERR_JAVA_EXCEPTION = 6 };
+enum { SP_DEL = 0, SP_DUP = 1, SP_INS = 2, SP_INV = 3 }; /* BuildModel.SV_TYPES, src/BuildModel.java:837 */
+
+/* ---- context --------------------------------------------------------------------------------------- */
+/* Replaces `private static Random random = new Random()` (src/SimulateHaplotypes.java:71): the seed is the one
+ * documented deviation from the reference argv. device = CUDA ordinal. */
+int sp_create(sp_ctx** out, int device, int64_t seed);
+void sp_destroy(sp_ctx* ctx);
+const char* sp_last_error(const sp_ctx* ctx);
+const char* sp_version(void);
+/* Launch on the caller's CUDA stream (cudaStream_t as void*); NULL = the context's own stream. */
+int sp_set_stream(sp_ctx* ctx, void* cuda_stream);
+/* Number of kernels this library launched on ctx since creation (bench.py's gpu_launches). */
+int64_t sp_kernel_launches(const sp_ctx* ctx);
+
+/* ---- row A1: reference ------------------------------------------------------------------------------ */
+/* SimulateHaplotypes.loadReference(String) (src/SimulateHaplotypes.java:119-134): skip one header line, trim and
+ * concatenate the rest; bytes go to HBM once. */
+int sp_load_reference_fasta(sp_ctx* ctx, const char* path);
+/* Same, from bytes already in host memory (one byte per base, case preserved). */
+int sp_set_reference(sp_ctx* ctx, const uint8_t* bases, int64_t length);
+int64_t sp_reference_length(const sp_ctx* ctx);
+
+/* ---- row V0: variant table + per-haplotype lists ------------------------------------------------------ */
+/* The `variants` array and `haplotype2variants[_last]` (src/SimulateHaplotypes.java:52-60) as SoA + CSR.
+ * payload_off has n+1 entries into payload_blob (INS sequence, already oriented, :809-810); has_payload[i]==0
+ * means sequence==null (an INS without payload splices the literal "null", as StringBuilder.append(null) does). */
+int sp_set_variants(sp_ctx* ctx, int32_t n, const int8_t* sv_type, const int32_t* position, const int32_t* length,
+                    const int64_t* payload_off, const uint8_t* payload_blob, const int8_t* has_payload);
+int sp_set_haplotype_lists(sp_ctx* ctx, int32_t n_haplotypes, const int64_t* list_off, const int32_t* ids);
+/* SimulateHaplotypes.deserialize(String,String) (src/SimulateHaplotypes.java:1147-1178). */
+int sp_load_population(sp_ctx* ctx, const char* haplotype2variants_file, const char* variants_file);
+
+/* ---- row M: haplotype materialisation ----------------------------------------------------------------- */
+/* SimulateHaplotypes.buildHaplotypes(first,last,outDir,buffer) (src/SimulateHaplotypes.java:917-960), split in
+ * (1) plan = edit lists -> segment tables by a segmented exclusive scan, (2) materialise = tiled copy kernel.
+ * Haplotypes [first..last] (inclusive, as the Java) become device-resident slots of `*slot_stride` bytes each.
+ * fasta_framing!=0 lays out the exact bytes of haplotype_<i>.fa (">chr1_<i>\n" + sequence + "\n") in the slot.
+ * out_lengths (host, last-first+1 entries): bytes of each slot that are meaningful (framed length). */
+int sp_plan_haplotypes(sp_ctx* ctx, int32_t first, int32_t last, int32_t fasta_framing, int64_t* out_lengths,
+                       int64_t* slot_stride);
+int sp_materialise(sp_ctx* ctx); /* asynchronous on the context's stream */
+int sp_synchronize(sp_ctx* ctx);
+/* Device pointer/length of the sequence (framing excluded) of planned haplotype h: input of the read kernel. */
+int sp_haplotype_device(sp_ctx* ctx, int32_t h, void** device_ptr, int64_t* sequence_length);
+/* D2H of the framed bytes of haplotype h. */
+int sp_copy_haplotype(sp_ctx* ctx, int32_t h, uint8_t* host_out, int64_t capacity, int64_t* written);
+/* plan + materialise + D2H of all of [first..last] into one host buffer, back to back (offsets: n+1 entries). */
+int sp_build_haplotypes_host(sp_ctx* ctx, int32_t first, int32_t last, int32_t fasta_framing, uint8_t* host_out,
+                             int64_t capacity, int64_t* offsets);
+/* PrintHaplotypes.main (src/PrintHaplotypes.java:6-18): writes OUTPUT_DIR/haplotype_<i>.fa. */
+int sp_print_haplotypes(sp_ctx* ctx, int32_t first, int32_t last, const char* reference_file,
+                        const char* haplotype2variants_file, const char* variants_file, const char* output_dir);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

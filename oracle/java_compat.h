@@ -97,7 +97,7 @@ inline std::string doubleToString(double d) {
     if (d == 0.0) return std::signbit(d) ? "-0.0" : "0.0";
     char buf[64];
     int prec;
-    for (prec = 0; prec < 17; prec++) {
+    for (prec = 1; prec < 17; prec++) {  // at least two significant digits (4.9E-324)
         snprintf(buf, sizeof buf, "%.*e", prec, d);
         if (strtod(buf, nullptr) == d) break;
     }

@@ -1,0 +1,101 @@
+// Shared internals of libsynthpop_cuda.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "../../include/synthpop_cuda.h"
+
+namespace sp {
+
+struct Error : std::runtime_error {
+    int code;
+    Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+#define SP_CUDA(call)                                                                                      \
+    do {                                                                                                   \
+        cudaError_t e__ = (call);                                                                          \
+        if (e__ != cudaSuccess)                                                                            \
+            throw sp::Error(SP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__) + " (" +     \
+                                             __FILE__ + ":" + std::to_string(__LINE__) + ")");            \
+    } while (0)
+
+// Device buffer with capacity-only growth (no shrink); contents are not preserved across grow().
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;  // elements
+    void reserve(size_t n, size_t slack_bytes = 64) {
+        if (n <= cap && p) return;
+        release();
+        SP_CUDA(cudaMalloc((void**)&p, n * sizeof(T) + slack_bytes));
+        cap = n;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+    }
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+// Segment source encoding (seg_src, int64): bits 62..60 = kind, bits 47..0 = byte offset in that space.
+enum SegKind : int { SEG_REF_FWD = 0, SEG_REF_RC = 1, SEG_PAYLOAD = 2, SEG_AUX = 3, SEG_PAD = 4 };
+constexpr int SEG_KIND_SHIFT = 60;
+constexpr int64_t SEG_OFF_MASK = (int64_t(1) << 48) - 1;
+
+constexpr int TILE_BYTES = 16384;  // output bytes per CTA tile of the materialisation kernel
+
+}  // namespace sp
+
+struct sp_ctx {
+    int device = 0;
+    int64_t seed = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int64_t launches = 0;
+    int sm_count = 148;
+
+    // row A1
+    std::vector<uint8_t> h_ref;
+    sp::DevBuf<uint8_t> d_ref;
+    int64_t ref_len = 0;
+
+    // row V0
+    int32_t n_variants = 0;
+    std::vector<int8_t> h_type;
+    std::vector<int32_t> h_pos, h_len;
+    std::vector<int64_t> h_payload_off;
+    std::vector<uint8_t> h_payload;
+    sp::DevBuf<int8_t> d_type;
+    sp::DevBuf<int32_t> d_pos, d_len;
+    sp::DevBuf<int64_t> d_payload_off;
+    sp::DevBuf<uint8_t> d_payload;
+    int32_t n_haplotypes = 0;
+    std::vector<int64_t> h_list_off;
+    std::vector<int32_t> h_list_ids;
+    sp::DevBuf<int64_t> d_list_off;
+    sp::DevBuf<int32_t> d_list_ids;
+
+    // row M plan (current batch of haplotypes [plan_first..plan_last])
+    int32_t plan_first = 0, plan_last = -1;
+    int32_t plan_framing = 0;
+    int64_t slot_stride = 0;
+    int64_t tiles_per_slot = 0;
+    std::vector<int64_t> h_hap_len;      // framed lengths
+    std::vector<int32_t> h_hdr_len;      // header bytes preceding the sequence in each slot
+    sp::DevBuf<int64_t> d_seg_dst, d_seg_src, d_seg_base, d_hap_len;
+    sp::DevBuf<int32_t> d_tile_first;
+    sp::DevBuf<uint8_t> d_aux;
+    sp::DevBuf<int64_t> d_aux_off;
+    sp::DevBuf<int32_t> d_err;
+    sp::DevBuf<uint8_t> d_out;
+    bool materialised = false;
+};

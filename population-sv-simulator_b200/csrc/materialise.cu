@@ -1,0 +1,377 @@
+// Row M of SURVEY.md §8a — haplotype materialisation (SimulateHaplotypes.buildHaplotypes,
+// reference src/SimulateHaplotypes.java:917-960), re-designed for B200:
+//
+//   plan_kernel ......... one CTA per haplotype; every edit of the sorted edit list becomes three segment
+//                         slots (reference gap, body, second DUP copy) and a block-wide exclusive scan over the
+//                         per-edit output deltas yields each segment's destination offset (the "segmented scan").
+//   tile_table_kernel ... one thread per 16 KiB output tile: index of the first segment that intersects it.
+//   materialise_kernel .. one CTA per output tile, tiles ordered region-major across the haplotypes of the
+//                         batch so that the reference window they share stays in the 126 MB L2; 16-byte
+//                         aligned streaming stores; the arbitrary byte shift between source and destination
+//                         is resolved in registers (two aligned 16-byte loads + funnel shifts).
+//
+// HBM-bound: 1 B read + 1 B written per output base (2 B/bp algorithmic).
+#include "common.cuh"
+
+namespace sp {
+
+__device__ __forceinline__ uint8_t complement_base(uint8_t c) {  // reverseComplement, :886-896
+    switch (c) {
+        case 'a': return 't'; case 'c': return 'g'; case 'g': return 'c'; case 't': return 'a';
+        case 'A': return 'T'; case 'C': return 'G'; case 'G': return 'C'; case 'T': return 'A';
+        default: return 'N';
+    }
+}
+
+// Exclusive scan of one int64 per thread over a 256-thread CTA; returns the exclusive prefix, total in `total`.
+__device__ __forceinline__ int64_t block_exclusive_scan_256(int64_t v, int64_t* warp_sums /*[8]*/, int64_t& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int64_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    int64_t warp_prefix = 0, t = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        int64_t s = warp_sums[w];
+        if (w < warp) warp_prefix += s;
+        t += s;
+    }
+    total = t;
+    __syncthreads();
+    return warp_prefix + incl - v;
+}
+
+// err[0] = code (1 bad variant id, 2 negative gap / start>end, 3 end beyond reference, 4 bad type), err[1] = haplotype,
+// err[2] = index in list.
+__global__ void __launch_bounds__(256)
+plan_kernel(const int8_t* __restrict__ type, const int32_t* __restrict__ pos, const int32_t* __restrict__ len,
+            const int64_t* __restrict__ payload_off, int32_t n_variants, const int64_t* __restrict__ list_off,
+            const int32_t* __restrict__ ids, int64_t ref_len, int first_hap, const int64_t* __restrict__ aux_off,
+            const int64_t* __restrict__ seg_base, int64_t* __restrict__ seg_dst, int64_t* __restrict__ seg_src,
+            int64_t* __restrict__ hap_len, int32_t* __restrict__ err) {
+    __shared__ int64_t warp_sums[8];
+    __shared__ int64_t carry_s;
+    const int hb = blockIdx.x, h = first_hap + hb, tid = threadIdx.x;
+    const int64_t lo = list_off[h], n = list_off[h + 1] - lo;
+    const int64_t sb = seg_base[hb];
+    const int64_t hdr_off = aux_off[hb], hdr_len = aux_off[hb + 1] - hdr_off;
+    if (tid == 0) {
+        seg_dst[sb] = 0;
+        seg_src[sb] = (int64_t(SEG_AUX) << SEG_KIND_SHIFT) | hdr_off;
+        carry_s = hdr_len;
+    }
+    __syncthreads();
+    auto fail = [&](int code, int64_t k) {
+        if (atomicCAS(&err[0], 0, code) == 0) { err[1] = h; err[2] = (int32_t)k; }
+    };
+    for (int64_t base = 0; base < n; base += 256) {
+        const int64_t k = base + tid;
+        int64_t gap = 0, b1 = 0, b2 = 0, src_gap = 0, src_b1 = 0, src_b2 = 0;
+        if (k < n) {
+            const int32_t id = ids[lo + k];
+            if (id < 0 || id >= n_variants) fail(1, k);
+            else {
+                const int t = type[id];
+                const int64_t p = pos[id], l = len[id];
+                int64_t prev_after = 0;
+                if (k > 0) {
+                    const int32_t pid = ids[lo + k - 1];
+                    if (pid >= 0 && pid < n_variants)
+                        prev_after = (type[pid] == SP_INS) ? (int64_t)pos[pid] : (int64_t)pos[pid] + len[pid];
+                }
+                gap = p - prev_after;
+                // out.append(reference,firstInReference,variant.position) throws unless 0<=start<=end<=length
+                if (gap < 0 || prev_after < 0) { fail(2, k); gap = 0; }
+                else if (p > ref_len) { fail(3, k); gap = 0; }
+                src_gap = (int64_t(SEG_REF_FWD) << SEG_KIND_SHIFT) | (prev_after & SEG_OFF_MASK);
+                if (t == SP_DEL) {
+                } else if (t == SP_DUP || t == SP_INV) {
+                    if (l < 0) fail(2, k);
+                    else if (p + l > ref_len) fail(3, k);
+                    else if (t == SP_DUP) {
+                        b1 = l; b2 = l;
+                        src_b1 = src_b2 = (int64_t(SEG_REF_FWD) << SEG_KIND_SHIFT) | p;
+                    } else {
+                        b1 = l;
+                        src_b1 = (int64_t(SEG_REF_RC) << SEG_KIND_SHIFT) | ((p + l - 1) & SEG_OFF_MASK);
+                    }
+                } else if (t == SP_INS) {
+                    b1 = payload_off[id + 1] - payload_off[id];
+                    src_b1 = (int64_t(SEG_PAYLOAD) << SEG_KIND_SHIFT) | payload_off[id];
+                } else fail(4, k);
+            }
+        }
+        int64_t total;
+        const int64_t excl = block_exclusive_scan_256(gap + b1 + b2, warp_sums, total) + carry_s;
+        if (k < n) {
+            const int64_t s = sb + 1 + 3 * k;
+            seg_dst[s] = excl;            seg_src[s] = src_gap;
+            seg_dst[s + 1] = excl + gap;  seg_src[s + 1] = src_b1;
+            seg_dst[s + 2] = excl + gap + b1;  seg_src[s + 2] = src_b2;
+        }
+        __syncthreads();
+        if (tid == 0) carry_s += total;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        int64_t last_after = 0;
+        if (n > 0) {
+            const int32_t pid = ids[lo + n - 1];
+            if (pid >= 0 && pid < n_variants)
+                last_after = (type[pid] == SP_INS) ? (int64_t)pos[pid] : (int64_t)pos[pid] + len[pid];
+        }
+        int64_t c = carry_s;
+        const int64_t s = sb + 1 + 3 * n;
+        const int64_t tail = last_after < ref_len ? ref_len - last_after : 0;  // :953
+        seg_dst[s] = c;  seg_src[s] = (int64_t(SEG_REF_FWD) << SEG_KIND_SHIFT) | (last_after & SEG_OFF_MASK);
+        c += tail;
+        seg_dst[s + 1] = c;  seg_src[s + 1] = (int64_t(SEG_AUX) << SEG_KIND_SHIFT) | 0;  // "\n" (bw.newLine, :956)
+        c += hdr_len > 0 ? 1 : 0;
+        seg_dst[s + 2] = c;  seg_src[s + 2] = int64_t(SEG_PAD) << SEG_KIND_SHIFT;
+        seg_dst[s + 3] = INT64_MAX;  seg_src[s + 3] = int64_t(SEG_PAD) << SEG_KIND_SHIFT;
+        hap_len[hb] = c;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+tile_table_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict__ seg_base, int n_hap,
+                  int64_t tiles_per_slot, int32_t* __restrict__ tile_first) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= tiles_per_slot * n_hap) return;
+    const int hb = (int)(idx / tiles_per_slot);
+    const int64_t x = (idx % tiles_per_slot) * TILE_BYTES;
+    const int64_t sb = seg_base[hb];
+    int64_t lo = 0, hi = seg_base[hb + 1] - sb;  // first local index with dst > x
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (seg_dst[sb + mid] <= x) lo = mid + 1; else hi = mid;
+    }
+    tile_first[idx] = (int32_t)(lo - 1);
+}
+
+__device__ __forceinline__ uint4 shift_combine(uint4 A, uint4 B, unsigned m) {
+    const unsigned s = (m & 3u) * 8u;
+    uint32_t x0, x1, x2, x3, x4;
+    switch (m >> 2) {
+        case 0: x0 = A.x; x1 = A.y; x2 = A.z; x3 = A.w; x4 = B.x; break;
+        case 1: x0 = A.y; x1 = A.z; x2 = A.w; x3 = B.x; x4 = B.y; break;
+        case 2: x0 = A.z; x1 = A.w; x2 = B.x; x3 = B.y; x4 = B.z; break;
+        default: x0 = A.w; x1 = B.x; x2 = B.y; x3 = B.z; x4 = B.w; break;
+    }
+    return make_uint4(__funnelshift_r(x0, x1, s), __funnelshift_r(x1, x2, s), __funnelshift_r(x2, x3, s),
+                      __funnelshift_r(x3, x4, s));
+}
+
+// 16 bytes starting at an arbitrary address (buffers carry >= 32 bytes of slack past their end).
+__device__ __forceinline__ uint4 load16_any(const uint8_t* p) {
+    const uintptr_t a = (uintptr_t)p;
+    const unsigned m = (unsigned)(a & 15u);
+    const uint4* q = (const uint4*)(a - m);
+    const uint4 A = __ldg(q);
+    if (m == 0) return A;
+    const uint4 B = __ldg(q + 1);
+    return shift_combine(A, B, m);
+}
+
+constexpr int MAX_TILE_SEGS = 96;
+
+__global__ void __launch_bounds__(256)
+materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload,
+                   const uint8_t* __restrict__ aux, const int64_t* __restrict__ seg_dst,
+                   const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
+                   const int32_t* __restrict__ tile_first, uint8_t* __restrict__ out, int64_t stride,
+                   int64_t tiles_per_slot, int n_hap) {
+    // region-major order: consecutive CTAs work on the same tile index of different haplotypes
+    const int64_t b = blockIdx.x;
+    const int hb = (int)(b % n_hap);
+    const int64_t t = b / n_hap;
+    const int64_t x0 = t * TILE_BYTES;
+    const int64_t sb = seg_base[hb];
+    const int64_t ti = (int64_t)hb * tiles_per_slot + t;
+    const int s0 = tile_first[ti];
+    const int s_last = (int)(seg_base[hb + 1] - sb) - 2;  // the PAD segment
+    int s1 = (t + 1 < tiles_per_slot) ? tile_first[ti + 1] : s_last;
+    if (s1 > s_last) s1 = s_last;
+    uint8_t* __restrict__ dst_tile = out + (int64_t)hb * stride + x0;
+    const int tid = threadIdx.x;
+
+    // does segment s1 start at or beyond the end of this tile? then it does not intersect it
+    const int64_t d0 = seg_dst[sb + s0];
+    const int64_t src0 = seg_src[sb + s0];
+    const int64_t d1 = seg_dst[sb + s0 + 1];
+    if (d1 >= x0 + TILE_BYTES) {
+        // ---- uniform path: the whole tile lies inside one segment
+        const int kind = (int)(src0 >> SEG_KIND_SHIFT);
+        const int64_t off = (src0 & SEG_OFF_MASK) + (x0 - d0);
+        if (kind == SEG_PAD) return;
+        if (kind != SEG_REF_RC) {
+            const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
+            const uint8_t* p = base + off;
+            const unsigned m = (unsigned)((uintptr_t)p & 15u);
+            const uint4* q = (const uint4*)(p - m);
+            uint4* o = (uint4*)dst_tile;
+            if (m == 0) {
+                uint4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) v[u] = __ldg(q + u * 256 + tid);
+#pragma unroll
+                for (int u = 0; u < 4; u++) __stcs(o + u * 256 + tid, v[u]);
+            } else {
+                uint4 A[4], B[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) { A[u] = __ldg(q + u * 256 + tid); B[u] = __ldg(q + u * 256 + tid + 1); }
+#pragma unroll
+                for (int u = 0; u < 4; u++) __stcs(o + u * 256 + tid, shift_combine(A[u], B[u], m));
+            }
+            return;
+        }
+    }
+
+    // ---- general path: several segments (or a reverse-complemented one) intersect the tile
+    __shared__ int64_t s_dst[MAX_TILE_SEGS + 1];
+    __shared__ int64_t s_src[MAX_TILE_SEGS];
+    const int nseg = s1 - s0 + 1;
+    const bool in_smem = nseg <= MAX_TILE_SEGS;
+    if (in_smem) {
+        for (int i = tid; i <= nseg; i += 256) s_dst[i] = seg_dst[sb + s0 + i];
+        for (int i = tid; i < nseg; i += 256) s_src[i] = seg_src[sb + s0 + i];
+    }
+    __syncthreads();
+    const int64_t* gd = seg_dst + sb + s0;
+    const int64_t* gs = seg_src + sb + s0;
+    auto DST = [&](int i) -> int64_t { return in_smem ? s_dst[i] : gd[i]; };
+    auto SRC = [&](int i) -> int64_t { return in_smem ? s_src[i] : gs[i]; };
+    for (int c = tid; c < TILE_BYTES / 16; c += 256) {
+        const int64_t x = x0 + (int64_t)c * 16;
+        int lo = 0, hi = nseg;  // last i in [0,nseg) with DST(i) <= x   (DST(0) <= x0 always)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (DST(mid) <= x) lo = mid; else hi = mid;
+        }
+        int i = lo;
+        int64_t src = SRC(i);
+        int kind = (int)(src >> SEG_KIND_SHIFT);
+        int64_t dnext = DST(i + 1);
+        uint4 v;
+        if (x + 16 <= dnext && kind != SEG_REF_RC) {
+            if (kind == SEG_PAD) continue;
+            const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
+            v = load16_any(base + (src & SEG_OFF_MASK) + (x - DST(i)));
+        } else {
+            uint32_t w[4] = {0, 0, 0, 0};
+            int64_t dcur = DST(i);
+            bool any = false;
+#pragma unroll 1
+            for (int j = 0; j < 16; j++) {
+                const int64_t xb = x + j;
+                while (xb >= dnext) {  // zero-length segments are skipped here as well
+                    i++;
+                    dcur = dnext; dnext = DST(i + 1); src = SRC(i);
+                    kind = (int)(src >> SEG_KIND_SHIFT);
+                }
+                uint8_t byte = 0;
+                const int64_t o = (src & SEG_OFF_MASK);
+                if (kind == SEG_REF_FWD) byte = ref[o + (xb - dcur)];
+                else if (kind == SEG_REF_RC) byte = complement_base(ref[o - (xb - dcur)]);
+                else if (kind == SEG_PAYLOAD) byte = payload[o + (xb - dcur)];
+                else if (kind == SEG_AUX) byte = aux[o + (xb - dcur)];
+                if (kind != SEG_PAD) any = true;
+                w[j >> 2] |= (uint32_t)byte << ((j & 3) * 8);
+            }
+            if (!any) continue;
+            v = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        __stcs((uint4*)(dst_tile + (int64_t)c * 16), v);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------- host
+static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride) {
+    if (c->ref_len <= 0) throw Error(SP_ERR_ARG, "no reference loaded");
+    if (c->n_haplotypes <= 0) throw Error(SP_ERR_ARG, "no haplotype lists loaded");
+    if (first < 0 || last >= c->n_haplotypes || first > last)
+        throw Error(SP_ERR_JAVA_EXCEPTION, "ArrayIndexOutOfBoundsException: haplotype range [" + std::to_string(first) + ".." + std::to_string(last) + "]");
+    const int nh = last - first + 1;
+    c->materialised = false;
+    // aux blob: "\n" at offset 0, then the FASTA headers ">chr1_<i>\n" (src/SimulateHaplotypes.java:955)
+    std::vector<uint8_t> aux(1, (uint8_t)'\n');
+    std::vector<int64_t> aux_off(nh + 1);
+    c->h_hdr_len.assign(nh, 0);
+    for (int i = 0; i < nh; i++) {
+        aux_off[i] = (int64_t)aux.size();
+        if (framing) {
+            std::string hdr = ">chr1_" + std::to_string(first + i) + "\n";
+            aux.insert(aux.end(), hdr.begin(), hdr.end());
+            c->h_hdr_len[i] = (int32_t)hdr.size();
+        }
+    }
+    aux_off[nh] = (int64_t)aux.size();
+    std::vector<int64_t> seg_base(nh + 1);
+    const int64_t l0 = c->h_list_off[first];
+    for (int i = 0; i <= nh; i++) seg_base[i] = 3 * (c->h_list_off[first + i] - l0) + 5 * (int64_t)i;
+    const int64_t nseg = seg_base[nh];
+    c->d_aux.reserve(aux.size());
+    c->d_aux_off.reserve(nh + 1);
+    c->d_seg_base.reserve(nh + 1);
+    c->d_seg_dst.reserve(nseg);
+    c->d_seg_src.reserve(nseg);
+    c->d_hap_len.reserve(nh);
+    c->d_err.reserve(4);
+    cudaStream_t st = c->stream;
+    SP_CUDA(cudaMemcpyAsync(c->d_aux.p, aux.data(), aux.size(), cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaMemcpyAsync(c->d_aux_off.p, aux_off.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaMemcpyAsync(c->d_seg_base.p, seg_base.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaMemsetAsync(c->d_err.p, 0, 16, st));
+    plan_kernel<<<nh, 256, 0, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, c->d_payload_off.p, c->n_variants,
+                                    c->d_list_off.p, c->d_list_ids.p, c->ref_len, first, c->d_aux_off.p,
+                                    c->d_seg_base.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_hap_len.p, c->d_err.p);
+    c->launches++;
+    SP_CUDA(cudaGetLastError());
+    c->h_hap_len.assign(nh, 0);
+    int32_t err[4] = {0, 0, 0, 0};
+    SP_CUDA(cudaMemcpyAsync(c->h_hap_len.data(), c->d_hap_len.p, nh * 8, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(err, c->d_err.p, 16, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaStreamSynchronize(st));
+    if (err[0] != 0) {
+        static const char* what[] = {"", "ArrayIndexOutOfBoundsException: variant id", "IndexOutOfBoundsException: start > end",
+                                     "IndexOutOfBoundsException: end > reference length", "invalid svType"};
+        throw Error(err[0] == 4 ? SP_ERR_ARG : SP_ERR_JAVA_EXCEPTION,
+                    std::string(what[err[0]]) + " (haplotype " + std::to_string(err[1]) + ", list index " + std::to_string(err[2]) + ")");
+    }
+    int64_t mx = 0;
+    for (int i = 0; i < nh; i++) mx = std::max(mx, c->h_hap_len[i]);
+    c->slot_stride = round_up(std::max<int64_t>(mx, 1), TILE_BYTES);
+    c->tiles_per_slot = c->slot_stride / TILE_BYTES;
+    const int64_t ntiles = c->tiles_per_slot * nh;
+    if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "batch too large: reduce the haplotype range");
+    c->d_tile_first.reserve(ntiles);
+    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(c->d_seg_dst.p, c->d_seg_base.p, nh,
+                                                                        c->tiles_per_slot, c->d_tile_first.p);
+    c->launches++;
+    SP_CUDA(cudaGetLastError());
+    c->d_out.reserve((size_t)c->slot_stride * nh);
+    c->plan_first = first; c->plan_last = last; c->plan_framing = framing;
+    if (out_lengths) for (int i = 0; i < nh; i++) out_lengths[i] = c->h_hap_len[i];
+    if (slot_stride) *slot_stride = c->slot_stride;
+}
+
+void materialise(sp_ctx* c) {
+    if (c->plan_last < c->plan_first) throw Error(SP_ERR_ARG, "sp_plan_haplotypes has not been called");
+    const int nh = c->plan_last - c->plan_first + 1;
+    const int64_t ntiles = c->tiles_per_slot * nh;
+    materialise_kernel<<<(unsigned)ntiles, 256, 0, c->stream>>>(c->d_ref.p, c->d_payload.p, c->d_aux.p, c->d_seg_dst.p,
+                                                                c->d_seg_src.p, c->d_seg_base.p, c->d_tile_first.p,
+                                                                c->d_out.p, c->slot_stride, c->tiles_per_slot, nh);
+    c->launches++;
+    SP_CUDA(cudaGetLastError());
+    c->materialised = true;
+}
+
+}  // namespace sp

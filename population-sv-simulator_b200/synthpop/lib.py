@@ -1,0 +1,207 @@
+"""ctypes binding of libsynthpop_cuda.so (the C ABI declared in include/synthpop_cuda.h).
+
+Host-side mirror of the reference's static-method interface for the hot path
+(SimulateHaplotypes.loadReference / deserialize / buildHaplotypes, PrintHaplotypes.main ...).
+There is no CPU fallback: if the CUDA extension is missing, importing `load()` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libsynthpop_cuda.so")
+
+SP_OK, SP_ERR, SP_ERR_COVERAGE, SP_ERR_CUDA, SP_ERR_ARG, SP_ERR_JAVA_EXCEPTION = 0, 1, 3, 4, 5, 6
+DEL, DUP, INS, INV = 0, 1, 2, 3
+
+_lib = None
+
+
+class SynthpopError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"[{code}] {message}")
+        self.code = code
+        self.message = message
+
+
+def _p(dtype):
+    return np.ctypeslib.ndpointer(dtype=dtype, flags="C_CONTIGUOUS")
+
+
+def load() -> C.CDLL:
+    """dlopen the in-tree libsynthpop_cuda.so and declare every prototype of include/synthpop_cuda.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64, cp = C.c_void_p, C.c_int32, C.c_int64, C.c_char_p
+    P = C.POINTER
+    sig = {
+        "sp_create": (C.c_int, [P(vp), C.c_int, i64]),
+        "sp_destroy": (None, [vp]),
+        "sp_last_error": (cp, [vp]),
+        "sp_version": (cp, []),
+        "sp_set_stream": (C.c_int, [vp, vp]),
+        "sp_kernel_launches": (i64, [vp]),
+        "sp_load_reference_fasta": (C.c_int, [vp, cp]),
+        "sp_set_reference": (C.c_int, [vp, vp, i64]),
+        "sp_reference_length": (i64, [vp]),
+        "sp_set_variants": (C.c_int, [vp, i32, vp, vp, vp, vp, vp, vp]),
+        "sp_set_haplotype_lists": (C.c_int, [vp, i32, vp, vp]),
+        "sp_load_population": (C.c_int, [vp, cp, cp]),
+        "sp_plan_haplotypes": (C.c_int, [vp, i32, i32, i32, vp, P(i64)]),
+        "sp_materialise": (C.c_int, [vp]),
+        "sp_synchronize": (C.c_int, [vp]),
+        "sp_haplotype_device": (C.c_int, [vp, i32, P(vp), P(i64)]),
+        "sp_copy_haplotype": (C.c_int, [vp, i32, vp, i64, P(i64)]),
+        "sp_build_haplotypes_host": (C.c_int, [vp, i32, i32, i32, vp, i64, vp]),
+        "sp_print_haplotypes": (C.c_int, [vp, i32, i32, cp, cp, cp, cp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    # optional entry points added by later rows; declared when present
+    lib._declared = set(sig)
+    _lib = lib
+    return lib
+
+
+def declared_symbols() -> list[str]:
+    """Every `sp_*` function declared in include/synthpop_cuda.h (parsed from the header)."""
+    import re
+    hdr = os.path.join(os.path.dirname(os.path.dirname(_HERE)), "include", "synthpop_cuda.h")
+    text = open(hdr).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(sp_[a-z0-9_]+)\s*\(", text)))
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One sp_ctx. Method names follow the reference's static methods."""
+
+    def __init__(self, device: int = 0, seed: int = 42):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.sp_create(C.byref(h), device, seed)
+        if rc != SP_OK:
+            raise SynthpopError(rc, "sp_create failed: no usable CUDA device (there is no CPU fallback)")
+        self.h = h
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.sp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != SP_OK:
+            raise SynthpopError(rc, (self.lib.sp_last_error(self.h) or b"").decode("utf-8", "replace"))
+
+    # -- plumbing
+    def set_stream(self, cuda_stream: int | None):
+        self._check(self.lib.sp_set_stream(self.h, C.c_void_p(cuda_stream or 0)))
+
+    def synchronize(self):
+        self._check(self.lib.sp_synchronize(self.h))
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.sp_kernel_launches(self.h))
+
+    # -- row A1
+    def load_reference(self, path: str):
+        """SimulateHaplotypes.loadReference (src/SimulateHaplotypes.java:119-134)."""
+        self._check(self.lib.sp_load_reference_fasta(self.h, path.encode()))
+
+    def set_reference(self, bases: np.ndarray):
+        bases = np.ascontiguousarray(bases, dtype=np.uint8)
+        self._check(self.lib.sp_set_reference(self.h, _ptr(bases), bases.size))
+
+    @property
+    def reference_length(self) -> int:
+        return int(self.lib.sp_reference_length(self.h))
+
+    # -- row V0
+    def set_variants(self, sv_type, position, length, payload_off=None, payload_blob=None, has_payload=None):
+        sv_type = np.ascontiguousarray(sv_type, dtype=np.int8)
+        position = np.ascontiguousarray(position, dtype=np.int32)
+        length = np.ascontiguousarray(length, dtype=np.int32)
+        n = sv_type.size
+        if payload_off is None:
+            payload_off = np.zeros(n + 1, dtype=np.int64)
+            payload_blob = np.zeros(1, dtype=np.uint8)
+        payload_off = np.ascontiguousarray(payload_off, dtype=np.int64)
+        payload_blob = np.ascontiguousarray(payload_blob, dtype=np.uint8)
+        hp = None if has_payload is None else np.ascontiguousarray(has_payload, dtype=np.int8)
+        self._check(self.lib.sp_set_variants(self.h, n, _ptr(sv_type), _ptr(position), _ptr(length),
+                                             _ptr(payload_off), _ptr(payload_blob), _ptr(hp)))
+
+    def set_haplotype_lists(self, list_off, ids):
+        list_off = np.ascontiguousarray(list_off, dtype=np.int64)
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        if ids.size == 0:
+            ids = np.zeros(1, dtype=np.int32)
+        self._check(self.lib.sp_set_haplotype_lists(self.h, list_off.size - 1, _ptr(list_off), _ptr(ids)))
+
+    def deserialize(self, haplotype2variants_file: str, variants_file: str):
+        """SimulateHaplotypes.deserialize (src/SimulateHaplotypes.java:1147-1178)."""
+        self._check(self.lib.sp_load_population(self.h, haplotype2variants_file.encode(), variants_file.encode()))
+
+    # -- row M
+    def plan_haplotypes(self, first: int, last: int, fasta_framing: bool = False):
+        n = max(0, last - first + 1)
+        lens = np.zeros(max(n, 1), dtype=np.int64)
+        stride = C.c_int64(0)
+        self._check(self.lib.sp_plan_haplotypes(self.h, first, last, int(fasta_framing), _ptr(lens), C.byref(stride)))
+        return lens[:n], int(stride.value)
+
+    def materialise(self):
+        self._check(self.lib.sp_materialise(self.h))
+
+    def haplotype_device(self, h: int):
+        p = C.c_void_p()
+        n = C.c_int64()
+        self._check(self.lib.sp_haplotype_device(self.h, h, C.byref(p), C.byref(n)))
+        return int(p.value or 0), int(n.value)
+
+    def copy_haplotype(self, h: int, capacity: int) -> np.ndarray:
+        out = np.empty(capacity, dtype=np.uint8)
+        w = C.c_int64()
+        self._check(self.lib.sp_copy_haplotype(self.h, h, _ptr(out), capacity, C.byref(w)))
+        return out[: w.value]
+
+    def build_haplotypes_host(self, first: int, last: int, out: np.ndarray, fasta_framing: bool = False):
+        """buildHaplotypes into one host buffer; returns offsets (n+1)."""
+        n = last - first + 1
+        offs = np.zeros(n + 1, dtype=np.int64)
+        self._check(self.lib.sp_build_haplotypes_host(self.h, first, last, int(fasta_framing), _ptr(out), out.size, _ptr(offs)))
+        return offs
+
+    def print_haplotypes(self, first: int, last: int, reference_file: str, haplotype2variants_file: str,
+                         variants_file: str, output_dir: str):
+        """PrintHaplotypes.main (src/PrintHaplotypes.java:6-18)."""
+        self._check(self.lib.sp_print_haplotypes(self.h, first, last, reference_file.encode(),
+                                                 haplotype2variants_file.encode(), variants_file.encode(),
+                                                 output_dir.encode()))
