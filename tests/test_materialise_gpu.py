@@ -65,7 +65,7 @@ def test_each_type_alone_and_edges(sp, oracle_lib):
     payload = np.frombuffer(b"ACGTTTGACCA" * 30, dtype=np.uint8).copy()
     #           DEL at 0   DUP      INS at 0-len gap  INV      INS at L (after the end)  DEL to the end
     sv_type = np.array([0, 1, 2, 3, 2, 0, 3], dtype=np.int8)
-    position = np.array([0, 100, 1000, 20_000, L, L - 70, 16], dtype=np.int32)
+    position = np.array([0, 100, 1000, 20_000, L, L - 70, 17], dtype=np.int32)
     length = np.array([17, 333, 200, 16_400, 130, 70, 1], dtype=np.int32)
     payload_off = np.array([0, 0, 0, 200, 200, 330, 330, 330], dtype=np.int64)
     lists = [np.array([i], np.int32) for i in range(7)] + [np.array([0, 6, 1, 2, 3], np.int32),
@@ -117,4 +117,29 @@ def test_print_haplotypes_files_match_oracle(sp, oracle_bin, tmp_path):
         assert a == b, f"haplotype_{i}.fa differs"
     with pytest.raises(sp.SynthpopError):
         ctx.print_haplotypes(6, 9, *args, got_dir)  # haplotype 8 does not exist: ArrayIndexOutOfBounds like the Java
+    ctx.close()
+
+
+def test_full_size_chr1_against_oracle(sp, oracle_lib):
+    """BASELINE configs[1] sizes (248 956 422 bp): bit-exact on sampled haplotypes, length identity on all of the batch."""
+    import bench
+    L = bench.CHR1
+    ref = bench.random_reference(L)
+    pop = bench.synth_population(L, 16)
+    ctx = sp.Context(0, 42)
+    ctx.set_reference(ref)
+    ctx.set_variants(pop["sv_type"], pop["position"], pop["length"], pop["payload_off"], pop["payload"])
+    ctx.set_haplotype_lists(pop["list_off"], pop["ids"])
+    lens, stride = ctx.plan_haplotypes(0, 15, False)
+    ctx.materialise()
+    ctx.synchronize()
+    t, ln = pop["sv_type"].astype(np.int64), pop["length"].astype(np.int64)
+    delta = np.where(t == 0, -ln, np.where(t == 3, 0, ln))  # DEL -len, DUP +len, INS +len, INV 0
+    for h in range(16):
+        assert lens[h] == L + int(delta[pop["lists"][h]].sum())
+    for h in (0, 7, 15):
+        want = oh.build_haplotype(oracle_lib, ref, pop["sv_type"], pop["position"], pop["length"], pop["payload_off"],
+                                  pop["payload"], None, pop["lists"][h])
+        got = ctx.copy_haplotype(h, int(stride))
+        assert np.array_equal(got, want), f"haplotype {h} differs at chr1 size"
     ctx.close()
