@@ -77,6 +77,53 @@ int sp_build_haplotypes_host(sp_ctx* ctx, int32_t first, int32_t last, int32_t f
 int sp_print_haplotypes(sp_ctx* ctx, int32_t first, int32_t last, const char* reference_file,
                         const char* haplotype2variants_file, const char* variants_file, const char* output_dir);
 
+/* ---- rows A2/A3/S1/G/C/N/I/R1/W/Z: SimulateHaplotypes ----------------------------------------------------- */
+/* Positional argv of SimulateHaplotypes.main (src/SimulateHaplotypes.java:76-86), same order and meaning. */
+typedef struct sp_population_args {
+    const char* model_dir;              /* args[0]  BuildModel.deserializeStatistics directory */
+    const char* population_name;        /* args[1]  ALL|AFR|AMR|EAS|EUR|OTH (resolved like Arrays.binarySearch, :101) */
+    const char* reference_file;         /* args[2] */
+    const char* repeat_intervals_file;  /* args[3] */
+    const char* segdups_file;           /* args[4] */
+    const char* insertion_strings_file; /* args[5] */
+    int32_t n_insertion_strings;        /* args[6] */
+    double allele_frequency_threshold;  /* args[7] */
+    int32_t n_variants_frequent;        /* args[8] */
+    int32_t n_individuals;              /* args[9] */
+    const char* output_dir;             /* args[10] */
+} sp_population_args;
+
+/* SimulateHaplotypes.main, whole run on one GPU: writes groundTruth_joint.vcf, groundTruth_individual_<2k>.vcf,
+ * haplotype2variants.txt, variants.txt, histogram_nVariantsPerHaplotype.txt, histogram_startPositions.txt into
+ * output_dir (:114-115, :715, :1014, :1028). Afterwards the context holds the reference, the variant table with
+ * payloads and every haplotype list, so sp_plan_haplotypes can follow without re-reading the files. */
+int sp_simulate_population(sp_ctx* ctx, const sp_population_args* args);
+
+/* The same run split at its one exchange point so that individuals can be sharded across GPUs
+ * (SURVEY.md §8e). begin: loadReference .. sampleVariants (replicated, same seed => same variants on every rank),
+ * then the genotype kernel + collision fixer + carrier counts for haplotypes [first_haplotype..last_haplotype] only
+ * (loop A :621-634 is index-addressable: cell (j,i) uses LCG steps S1+2(j*H+i)+1,+2). */
+int sp_population_begin(sp_ctx* ctx, const sp_population_args* args, int32_t first_haplotype, int32_t last_haplotype);
+/* n_variants = lastVariant+1, n_haplotypes = 2*N_INDIVIDUALS, local_entries = list entries of the local shard. */
+int sp_population_info(sp_ctx* ctx, int32_t* n_variants, int32_t* n_haplotypes, int64_t* local_entries,
+                       int32_t* n_local_haplotypes_with_collision);
+/* Per-variant carrier counts of the local shard: host copy, and the device buffer (int32[n_variants]) that the
+ * host's NCCL all-gather reads (the single inter-GPU exchange). */
+int sp_population_local_counts(sp_ctx* ctx, int32_t* counts);
+int sp_population_counts_device(sp_ctx* ctx, void** device_counts);
+/* Local haplotype lists after collision fixing (CSR: off has last-first+2 entries). */
+int sp_population_local_lists(sp_ctx* ctx, int64_t* off, int32_t* ids);
+/* Lists before collision fixing = the raw genotype matrix (row G), for kernel-level parity tests. */
+int sp_population_pre_collision_lists(sp_ctx* ctx, int64_t* off, int32_t* ids, int64_t ids_capacity, int64_t* n_ids);
+/* Draw-stream bookkeeping of the replicated prologue. */
+int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, int32_t* candidates);
+/* finish: AF := carriers/H and isActive from global_counts (NULL = the local counts are global), then
+ * assignInsertionStrings, annotateVariantsWithRepeats, the individual VCFs of the local shard and, when
+ * all_off/all_ids (CSR over ALL haplotypes) are given and write_joint_outputs!=0, the joint VCF, haplotype2variants.txt,
+ * variants.txt and the histograms. */
+int sp_population_finish(sp_ctx* ctx, const int32_t* global_counts, const int64_t* all_off, const int32_t* all_ids,
+                         int32_t write_joint_outputs);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,8 @@
 
 namespace sp {
 
+struct PopulationState;
+
 struct Error : std::runtime_error {
     int code;
     Error(int c, const std::string& m) : std::runtime_error(m), code(c) {}
@@ -29,11 +31,20 @@ template <class T>
 struct DevBuf {
     T* p = nullptr;
     size_t cap = 0;  // elements
-    void reserve(size_t n, size_t slack_bytes = 64) {
+    // headroom: fraction of extra capacity allocated when the buffer has to grow (avoids cudaFree/cudaMalloc
+    // ping-pong when successive batches differ slightly in size)
+    void reserve(size_t n, double headroom = 0.25, size_t slack_bytes = 64) {
         if (n <= cap && p) return;
         release();
-        SP_CUDA(cudaMalloc((void**)&p, n * sizeof(T) + slack_bytes));
-        cap = n;
+        const size_t want = n + (size_t)((double)n * headroom);
+        if (cudaMalloc((void**)&p, want * sizeof(T) + slack_bytes) != cudaSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+            SP_CUDA(cudaMalloc((void**)&p, n * sizeof(T) + slack_bytes));
+            cap = n;
+            return;
+        }
+        cap = want;
     }
     void release() {
         if (p) cudaFree(p);
@@ -98,4 +109,7 @@ struct sp_ctx {
     sp::DevBuf<int32_t> d_err;
     sp::DevBuf<uint8_t> d_out;
     bool materialised = false;
+
+    // rows S1/G/C/N/I/R1/W/Z: one SimulateHaplotypes run
+    sp::PopulationState* pop = nullptr;
 };

@@ -356,7 +356,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
                                                                         c->tiles_per_slot, c->d_tile_first.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());
-    c->d_out.reserve((size_t)c->slot_stride * nh);
+    c->d_out.reserve((size_t)c->slot_stride * nh, 0.01);
     c->plan_first = first; c->plan_last = last; c->plan_framing = framing;
     if (out_lengths) for (int i = 0; i < nh; i++) out_lengths[i] = c->h_hap_len[i];
     if (slot_stride) *slot_stride = c->slot_stride;

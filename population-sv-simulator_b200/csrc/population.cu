@@ -1,0 +1,241 @@
+// Orchestration and C ABI of one SimulateHaplotypes run (reference src/SimulateHaplotypes.java:75-116).
+#include "population.h"
+#include "java_random.cuh"
+#include "textio.h"
+#include <algorithm>
+#include <cmath>
+
+namespace sp {
+
+void free_population(sp_ctx* c) {
+    delete c->pop;
+    c->pop = nullptr;
+}
+
+static std::string need(const char* s, const char* what) {
+    if (!s) throw Error(SP_ERR_ARG, std::string("missing argument: ") + what);
+    return s;
+}
+
+// Ctx variant table (row V0) from the population's variants; payloads are set after assign_insertion_strings.
+static void publish_variants(sp_ctx* c, PopulationState& P) {
+    const int32_t n = P.n_variants;
+    c->n_variants = n;
+    c->h_type.resize(n); c->h_pos.resize(n); c->h_len.resize(n);
+    c->h_payload_off.assign((size_t)n + 1, 0);
+    c->h_payload.clear();
+    for (int32_t i = 0; i < n; i++) {
+        const VariantRec& v = P.variants[i];
+        c->h_type[i] = (int8_t)v.svType; c->h_pos[i] = v.position; c->h_len[i] = v.length;
+        if (v.hasSequence) c->h_payload.insert(c->h_payload.end(), P.payload.begin() + v.seq_off, P.payload.begin() + v.seq_off + v.seq_len);
+        else if (v.svType == SP_INS) { const char* s = "null"; c->h_payload.insert(c->h_payload.end(), s, s + 4); }
+        c->h_payload_off[i + 1] = (int64_t)c->h_payload.size();
+    }
+    c->d_type.reserve(std::max(n, 1)); c->d_pos.reserve(std::max(n, 1)); c->d_len.reserve(std::max(n, 1));
+    c->d_payload_off.reserve(n + 1);
+    c->d_payload.reserve(std::max<size_t>(c->h_payload.size(), 1));
+    cudaStream_t st = c->stream;
+    if (n > 0) {
+        SP_CUDA(cudaMemcpyAsync(c->d_type.p, c->h_type.data(), n, cudaMemcpyHostToDevice, st));
+        SP_CUDA(cudaMemcpyAsync(c->d_pos.p, c->h_pos.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+        SP_CUDA(cudaMemcpyAsync(c->d_len.p, c->h_len.data(), (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    }
+    SP_CUDA(cudaMemcpyAsync(c->d_payload_off.p, c->h_payload_off.data(), ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (!c->h_payload.empty())
+        SP_CUDA(cudaMemcpyAsync(c->d_payload.p, c->h_payload.data(), c->h_payload.size(), cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaStreamSynchronize(st));
+    c->plan_last = -1; c->plan_first = 0;
+}
+
+void population_begin(sp_ctx* c, const sp_population_args* a, int32_t first_h, int32_t last_h) {
+    if (!a) throw Error(SP_ERR_ARG, "null sp_population_args");
+    free_population(c);
+    c->pop = new PopulationState();
+    PopulationState& P = *c->pop;
+    P.model_dir = need(a->model_dir, "MODEL_DIR");
+    P.population_name = need(a->population_name, "POPULATION_NAME");
+    P.reference_file = need(a->reference_file, "REFERENCE_FILE");
+    P.repeats_file = need(a->repeat_intervals_file, "REPEAT_INTERVALS_FILE");
+    P.segdups_file = need(a->segdups_file, "SEGDUPS_FILE");
+    P.insertions_file = need(a->insertion_strings_file, "INSERTION_STRINGS_FILE");
+    P.output_dir = need(a->output_dir, "OUTPUT_DIR");
+    P.n_insertion_strings = a->n_insertion_strings;
+    P.af_threshold = a->allele_frequency_threshold;
+    P.n_frequent = a->n_variants_frequent;
+    P.n_individuals = a->n_individuals;
+    if (P.n_insertion_strings < 0) throw Error(SP_ERR_JAVA_EXCEPTION, "NegativeArraySizeException: N_INSERTION_STRINGS");
+    if (P.n_individuals < 0 || P.n_individuals > (INT32_MAX >> 1)) throw Error(SP_ERR_JAVA_EXCEPTION, "NegativeArraySizeException: N_INDIVIDUALS");
+    P.n_haplotypes_total = P.n_individuals << 1;
+    if (last_h < 0) last_h = P.n_haplotypes_total - 1;
+    if (first_h < 0 || first_h > last_h + 1 || last_h >= P.n_haplotypes_total) throw Error(SP_ERR_ARG, "bad haplotype shard");
+    P.h0 = first_h; P.h1 = last_h + 1;
+    P.keep_pre_collision = getenv("SYNTHPOP_KEEP_PRE_COLLISION") != nullptr;
+
+    load_reference_fasta(c, P.reference_file.c_str());                  // :93
+    P.model.load_statistics(P.model_dir);                               // :95
+    P.model.load_repeat_intervals(P.repeats_file);                      // :96
+    P.model.load_segdups(P.segdups_file);                               // :97
+    const int32_t L = (int32_t)c->ref_len;
+    P.positions.build(P.model, c->h_ref.data(), L, MAX_DISTANCE_SR);    // :99
+    sample_variants(P, c->seed, L);                                     // :101
+    publish_variants(c, P);
+    // nextDouble() <= AF  <=>  draw53 <= floor(AF * 2^53): both sides are exact in binary64
+    P.h_thr.resize(P.n_variants);
+    for (int32_t v = 0; v < P.n_variants; v++) {
+        const double af = P.variants[v].alleleFrequency;
+        int64_t t;
+        if (!(af >= 0.0)) t = -1;                       // negative (or NaN): never
+        else if (af >= 1.0) t = (int64_t)1 << 53;       // always
+        else t = (int64_t)std::floor(std::ldexp(af, 53));
+        P.h_thr[v] = t;
+    }
+    run_genotype_and_collisions(c, P);                                  // :104 (loops A and the collision fixer)
+    P.begun = true;
+}
+
+void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* all_off, const int32_t* all_ids, int32_t write_joint) {
+    if (!c->pop || !c->pop->begun) throw Error(SP_ERR_ARG, "sp_population_begin has not been called");
+    PopulationState& P = *c->pop;
+    const int32_t V = P.n_variants, H = P.n_haplotypes_total, L = (int32_t)c->ref_len;
+    const bool local_is_global = P.h0 == 0 && P.h1 == H;
+    if (!global_counts && !local_is_global) throw Error(SP_ERR_ARG, "a sharded run needs the all-gathered carrier counts");
+    P.counts_global.assign(V, 0);
+    for (int32_t v = 0; v < V; v++) P.counts_global[v] = global_counts ? global_counts[v] : P.h_counts_local[v];
+    if (all_off && all_ids) {
+        P.all_off.assign(all_off, all_off + H + 1);
+        P.all_ids.assign(all_ids, all_ids + all_off[H]);
+        P.have_all_lists = true;
+    } else if (local_is_global) {
+        P.all_off = P.h_off;
+        P.all_ids = P.h_ids;
+        P.have_all_lists = true;
+    }
+    // isActive (:693-697) and the empirical allele frequency (:986)
+    P.nVariants_frequent = 0; P.nVariants_rare = 0;
+    for (int32_t v = 0; v < V; v++) {
+        VariantRec& r = P.variants[v];
+        r.isActive = P.counts_global[v] > 0;
+        if (r.isActive) { if (r.alleleFrequency >= P.af_threshold) P.nVariants_frequent++; else P.nVariants_rare++; }
+    }
+    for (int32_t v = 0; v < V; v++) P.variants[v].alleleFrequency = ((double)(P.counts_global[v] - 1) + 1.0) / (double)H;
+    assign_insertion_strings(P, c->seed);                               // :107-109
+    annotate_variants_with_repeats(P, 100);                             // :111
+    if (write_joint) {
+        if (!P.have_all_lists) throw Error(SP_ERR_ARG, "the joint outputs need every haplotype's list");
+        write_histograms(P, L);
+        write_joint_vcf(P, c->h_ref.data(), L);
+    }
+    write_individual_vcfs(P, c->h_ref.data(), L, P.h0, P.h1 - 1, P.h_off.data(), P.h_ids.data(), P.h0);  // :1027-1066
+    if (write_joint) write_population_files(P);                        // :114
+    // leave the context ready for sp_plan_haplotypes: variant table with payloads + haplotype lists
+    publish_variants(c, P);
+    c->n_haplotypes = H;
+    if (P.have_all_lists) { c->h_list_off = P.all_off; c->h_list_ids = P.all_ids; }
+    else {
+        c->h_list_off.assign((size_t)H + 1, 0);
+        for (int32_t h = 0; h < H; h++) {
+            int64_t n = 0;
+            if (h >= P.h0 && h < P.h1) n = P.h_off[h - P.h0 + 1] - P.h_off[h - P.h0];
+            c->h_list_off[h + 1] = c->h_list_off[h] + n;
+        }
+        c->h_list_ids = P.h_ids;
+    }
+    c->d_list_off.reserve(H + 1);
+    c->d_list_ids.reserve(std::max<size_t>(c->h_list_ids.size(), 1));
+    SP_CUDA(cudaMemcpyAsync(c->d_list_off.p, c->h_list_off.data(), ((size_t)H + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    if (!c->h_list_ids.empty())
+        SP_CUDA(cudaMemcpyAsync(c->d_list_ids.p, c->h_list_ids.data(), c->h_list_ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    SP_CUDA(cudaStreamSynchronize(c->stream));
+}
+
+}  // namespace sp
+
+using sp::Error;
+
+#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { cudaSetDevice(ctx->device);
+#define SP_API_END                                                                         \
+    return SP_OK; }                                                                        \
+    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
+    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }
+
+static sp::PopulationState& pop_of(sp_ctx* ctx) {
+    if (!ctx->pop || !ctx->pop->begun) throw Error(SP_ERR_ARG, "sp_population_begin has not been called");
+    return *ctx->pop;
+}
+
+extern "C" {
+
+int sp_simulate_population(sp_ctx* ctx, const sp_population_args* args) {
+    SP_API_BEGIN
+    sp::population_begin(ctx, args, 0, -1);
+    sp::population_finish(ctx, nullptr, nullptr, nullptr, 1);
+    SP_API_END
+}
+
+int sp_population_begin(sp_ctx* ctx, const sp_population_args* args, int32_t first_haplotype, int32_t last_haplotype) {
+    SP_API_BEGIN
+    sp::population_begin(ctx, args, first_haplotype, last_haplotype);
+    SP_API_END
+}
+
+int sp_population_info(sp_ctx* ctx, int32_t* n_variants, int32_t* n_haplotypes, int64_t* local_entries, int32_t* n_fixed) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (n_variants) *n_variants = P.n_variants;
+    if (n_haplotypes) *n_haplotypes = P.n_haplotypes_total;
+    if (local_entries) *local_entries = P.h_off.empty() ? 0 : P.h_off.back();
+    if (n_fixed) *n_fixed = P.n_haplotypes_with_collision;
+    SP_API_END
+}
+
+int sp_population_local_counts(sp_ctx* ctx, int32_t* counts) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (P.n_variants > 0) memcpy(counts, P.h_counts_local.data(), (size_t)P.n_variants * 4);
+    SP_API_END
+}
+
+int sp_population_counts_device(sp_ctx* ctx, void** device_counts) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (device_counts) *device_counts = P.d_counts.p;
+    SP_API_END
+}
+
+int sp_population_local_lists(sp_ctx* ctx, int64_t* off, int32_t* ids) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (off) memcpy(off, P.h_off.data(), P.h_off.size() * 8);
+    if (ids && !P.h_ids.empty()) memcpy(ids, P.h_ids.data(), P.h_ids.size() * 4);
+    SP_API_END
+}
+
+int sp_population_pre_collision_lists(sp_ctx* ctx, int64_t* off, int32_t* ids, int64_t ids_capacity, int64_t* n_ids) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (!P.keep_pre_collision) throw Error(SP_ERR_ARG, "set SYNTHPOP_KEEP_PRE_COLLISION=1 before sp_population_begin");
+    if (n_ids) *n_ids = (int64_t)P.h_pre_ids.size();
+    if (off) memcpy(off, P.h_pre_off.data(), P.h_pre_off.size() * 8);
+    if (ids) {
+        if ((int64_t)P.h_pre_ids.size() > ids_capacity) throw Error(SP_ERR_ARG, "ids buffer too small");
+        if (!P.h_pre_ids.empty()) memcpy(ids, P.h_pre_ids.data(), P.h_pre_ids.size() * 4);
+    }
+    SP_API_END
+}
+
+int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, int32_t* candidates) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (steps_after_sample_variants) *steps_after_sample_variants = P.steps_after_sampling;
+    if (candidates) *candidates = P.candidates;
+    SP_API_END
+}
+
+int sp_population_finish(sp_ctx* ctx, const int32_t* global_counts, const int64_t* all_off, const int32_t* all_ids,
+                         int32_t write_joint_outputs) {
+    SP_API_BEGIN
+    sp::population_finish(ctx, global_counts, all_off, all_ids, write_joint_outputs);
+    SP_API_END
+}
+
+}  // extern "C"

@@ -27,7 +27,7 @@ int main(int argc, char** argv) {
         else break;
     }
     if (a >= argc) {
-        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <PrintHaplotypes> <positional argv of the Java class>\n");
+        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes> <positional argv of the Java class>\n");
         return 2;
     }
     const std::string cls = argv[a++];
@@ -41,6 +41,17 @@ int main(int argc, char** argv) {
     if (cls == "PrintHaplotypes") {
         if (args.size() < 6) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
         rc = sp_print_haplotypes(ctx, atoi(args[0]), atoi(args[1]), args[2], args[3], args[4], args[5]);
+    } else if (cls == "SimulateHaplotypes") {
+        // MODEL_DIR POPULATION_NAME REFERENCE_FILE REPEAT_INTERVALS_FILE SEGDUPS_FILE INSERTION_STRINGS_FILE
+        // N_INSERTION_STRINGS ALLELE_FREQUENCY_THRESHOLD N_VARIANTS_FREQUENT N_INDIVIDUALS OUTPUT_DIR
+        // (src/SimulateHaplotypes.java:76-86)
+        if (args.size() < 11) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
+        sp_population_args pa;
+        pa.model_dir = args[0]; pa.population_name = args[1]; pa.reference_file = args[2];
+        pa.repeat_intervals_file = args[3]; pa.segdups_file = args[4]; pa.insertion_strings_file = args[5];
+        pa.n_insertion_strings = atoi(args[6]); pa.allele_frequency_threshold = atof(args[7]);
+        pa.n_variants_frequent = atoi(args[8]); pa.n_individuals = atoi(args[9]); pa.output_dir = args[10];
+        rc = sp_simulate_population(ctx, &pa);
     } else {
         fprintf(stderr, "synthpop: unknown class %s\n", cls.c_str());
         sp_destroy(ctx);

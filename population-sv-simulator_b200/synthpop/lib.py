@@ -27,6 +27,23 @@ class SynthpopError(RuntimeError):
         self.message = message
 
 
+class PopulationArgs(C.Structure):
+    """sp_population_args: the positional argv of SimulateHaplotypes.main (src/SimulateHaplotypes.java:76-86)."""
+    _fields_ = [("model_dir", C.c_char_p), ("population_name", C.c_char_p), ("reference_file", C.c_char_p),
+                ("repeat_intervals_file", C.c_char_p), ("segdups_file", C.c_char_p),
+                ("insertion_strings_file", C.c_char_p), ("n_insertion_strings", C.c_int32),
+                ("allele_frequency_threshold", C.c_double), ("n_variants_frequent", C.c_int32),
+                ("n_individuals", C.c_int32), ("output_dir", C.c_char_p)]
+
+    @classmethod
+    def from_argv(cls, argv):
+        a = [str(x) for x in argv]
+        if len(a) < 11:
+            raise IndexError("SimulateHaplotypes takes 11 positional arguments")
+        return cls(a[0].encode(), a[1].encode(), a[2].encode(), a[3].encode(), a[4].encode(), a[5].encode(),
+                   int(a[6]), float(a[7]), int(a[8]), int(a[9]), a[10].encode())
+
+
 def _p(dtype):
     return np.ctypeslib.ndpointer(dtype=dtype, flags="C_CONTIGUOUS")
 
@@ -62,6 +79,15 @@ def load() -> C.CDLL:
         "sp_copy_haplotype": (C.c_int, [vp, i32, vp, i64, P(i64)]),
         "sp_build_haplotypes_host": (C.c_int, [vp, i32, i32, i32, vp, i64, vp]),
         "sp_print_haplotypes": (C.c_int, [vp, i32, i32, cp, cp, cp, cp]),
+        "sp_simulate_population": (C.c_int, [vp, P(PopulationArgs)]),
+        "sp_population_begin": (C.c_int, [vp, P(PopulationArgs), i32, i32]),
+        "sp_population_info": (C.c_int, [vp, P(i32), P(i32), P(i64), P(i32)]),
+        "sp_population_local_counts": (C.c_int, [vp, vp]),
+        "sp_population_counts_device": (C.c_int, [vp, P(vp)]),
+        "sp_population_local_lists": (C.c_int, [vp, vp, vp]),
+        "sp_population_pre_collision_lists": (C.c_int, [vp, vp, vp, i64, P(i64)]),
+        "sp_population_draw_log": (C.c_int, [vp, P(C.c_uint64), P(i32)]),
+        "sp_population_finish": (C.c_int, [vp, vp, vp, vp, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -205,3 +231,57 @@ class Context:
         self._check(self.lib.sp_print_haplotypes(self.h, first, last, reference_file.encode(),
                                                  haplotype2variants_file.encode(), variants_file.encode(),
                                                  output_dir.encode()))
+
+    # -- rows S1/G/C/N/I/R1/W/Z
+    def simulate_haplotypes(self, argv):
+        """SimulateHaplotypes.main(args) (src/SimulateHaplotypes.java:75-116): same positional argv."""
+        args = PopulationArgs.from_argv(argv)
+        self._check(self.lib.sp_simulate_population(self.h, C.byref(args)))
+
+    def population_begin(self, argv, first_haplotype: int = 0, last_haplotype: int = -1):
+        args = PopulationArgs.from_argv(argv)
+        self._check(self.lib.sp_population_begin(self.h, C.byref(args), first_haplotype, last_haplotype))
+
+    def population_info(self):
+        nv, nh, ne, nf = C.c_int32(), C.c_int32(), C.c_int64(), C.c_int32()
+        self._check(self.lib.sp_population_info(self.h, C.byref(nv), C.byref(nh), C.byref(ne), C.byref(nf)))
+        return dict(n_variants=nv.value, n_haplotypes=nh.value, local_entries=ne.value, n_fixed=nf.value)
+
+    def population_local_counts(self) -> np.ndarray:
+        info = self.population_info()
+        out = np.zeros(max(info["n_variants"], 1), dtype=np.int32)
+        self._check(self.lib.sp_population_local_counts(self.h, _ptr(out)))
+        return out[: info["n_variants"]]
+
+    def population_counts_device(self) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.sp_population_counts_device(self.h, C.byref(p)))
+        return int(p.value or 0)
+
+    def population_local_lists(self, n_local_haplotypes: int):
+        info = self.population_info()
+        off = np.zeros(n_local_haplotypes + 1, dtype=np.int64)
+        ids = np.zeros(max(info["local_entries"], 1), dtype=np.int32)
+        self._check(self.lib.sp_population_local_lists(self.h, _ptr(off), _ptr(ids)))
+        return off, ids[: info["local_entries"]]
+
+    def population_pre_collision_lists(self, n_local_haplotypes: int):
+        n = C.c_int64()
+        self._check(self.lib.sp_population_pre_collision_lists(self.h, None, None, 0, C.byref(n)))
+        off = np.zeros(n_local_haplotypes + 1, dtype=np.int64)
+        ids = np.zeros(max(n.value, 1), dtype=np.int32)
+        self._check(self.lib.sp_population_pre_collision_lists(self.h, _ptr(off), _ptr(ids), ids.size, C.byref(n)))
+        return off, ids[: n.value]
+
+    def population_draw_log(self):
+        s, c = C.c_uint64(), C.c_int32()
+        self._check(self.lib.sp_population_draw_log(self.h, C.byref(s), C.byref(c)))
+        return dict(steps_after_sample_variants=s.value, candidates=c.value)
+
+    def population_finish(self, global_counts=None, all_off=None, all_ids=None, write_joint_outputs: bool = True):
+        gc = None if global_counts is None else np.ascontiguousarray(global_counts, dtype=np.int32)
+        ao = None if all_off is None else np.ascontiguousarray(all_off, dtype=np.int64)
+        ai = None if all_ids is None else np.ascontiguousarray(all_ids, dtype=np.int32)
+        if ai is not None and ai.size == 0:
+            ai = np.zeros(1, dtype=np.int32)
+        self._check(self.lib.sp_population_finish(self.h, _ptr(gc), _ptr(ao), _ptr(ai), int(write_joint_outputs)))

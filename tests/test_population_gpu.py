@@ -1,0 +1,86 @@
+"""Rows S1/G/C/N/I/R1/W/Z parity: sp_simulate_population (CUDA genotype kernel + collision fixer + host prologue and
+writers, through the C ABI) against the CPU oracle's restatement of SimulateHaplotypes.main on the same seed and
+inputs. Every output file must be byte-identical."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+FILES = ["groundTruth_joint.vcf", "haplotype2variants.txt", "variants.txt", "histogram_nVariantsPerHaplotype.txt",
+         "histogram_startPositions.txt"]
+
+
+def _cmp_dirs(want, got, n_ind):
+    names = FILES + [f"groundTruth_individual_{2 * k}.vcf" for k in range(n_ind)]
+    for n in names:
+        a = open(os.path.join(want, n), "rb").read()
+        b = open(os.path.join(got, n), "rb").read()
+        if a != b:
+            k = next(i for i in range(min(len(a), len(b))) if a[i] != b[i]) if a[:min(len(a), len(b))] != b[:min(len(a), len(b))] else min(len(a), len(b))
+            raise AssertionError(f"{n} differs at byte {k}: want {a[max(0,k-60):k+60]!r} got {b[max(0,k-60):k+60]!r}")
+
+
+def _parse_lists(path):
+    rows = open(path).read().split("\n")
+    H = int(rows[0])
+    out = []
+    for r in rows[1:1 + H]:
+        t = r.split(",")
+        out.append(np.array([int(x) for x in t[1:1 + int(t[0]) + 1]], dtype=np.int32))
+    return out
+
+
+@pytest.mark.parametrize("L,n_ind,n_freq,seed", [(1_500_000, 5, 250, 42), (6_000_000, 16, 900, 7), (800_000, 3, 120, 123456789)])
+def test_simulate_haplotypes_outputs_byte_identical(sp, oracle_bin, tmp_path, L, n_ind, n_freq, seed):
+    from synthpop import synth
+    inp = synth.generate_population_inputs(str(tmp_path / "in"), L, n_insertions=2500, seed=seed)
+    want = str(tmp_path / "want"); got = str(tmp_path / "got")
+    os.makedirs(want); os.makedirs(got)
+    pre = str(tmp_path / "pre.txt"); log = str(tmp_path / "draws.txt")
+    subprocess.run([oracle_bin, "--quiet", "--seed", str(seed), "--dump-pre-collision", pre, "--draw-log", log,
+                    "SimulateHaplotypes"] + inp.simulate_argv(want, n_ind, n_frequent=n_freq), check=True)
+    os.environ["SYNTHPOP_KEEP_PRE_COLLISION"] = "1"
+    ctx = sp.Context(0, seed)
+    ctx.simulate_haplotypes(inp.simulate_argv(got, n_ind, n_frequent=n_freq))
+    # row S1: same number of candidates and LCG steps as the oracle's draw log
+    dl = dict(l.split("=") for l in open(log).read().split())
+    mine = ctx.population_draw_log()
+    assert mine["steps_after_sample_variants"] == int(dl["steps_after_sampleVariants"])
+    assert mine["candidates"] == int(dl["candidates"])
+    # row G: the raw genotype matrix (lists before collision fixing)
+    off, ids = ctx.population_pre_collision_lists(2 * n_ind)
+    for h, w in enumerate(_parse_lists(pre)):
+        assert np.array_equal(ids[off[h]:off[h + 1]], w), f"genotype row of haplotype {h} differs"
+    # rows C/N/I/R1/W/Z: every output file
+    _cmp_dirs(want, got, n_ind)
+    # the context is ready for materialisation: haplotypes equal the oracle's PrintHaplotypes
+    hw = str(tmp_path / "hw"); os.makedirs(hw)
+    subprocess.run([oracle_bin, "--quiet", "PrintHaplotypes", "0", "3", inp.reference_file, want + "/haplotype2variants.txt",
+                    want + "/variants.txt", hw], check=True)
+    lens, stride = ctx.plan_haplotypes(0, 3, True)
+    ctx.materialise()
+    for h in range(4):
+        assert ctx.copy_haplotype(h, stride).tobytes() == open(f"{hw}/haplotype_{h}.fa", "rb").read()
+    ctx.close()
+
+
+def test_sharded_population_matches_single(sp, oracle_bin, tmp_path):
+    """Two 'ranks' on one GPU, run one after the other: shard [0..5] and [6..11], exchange counts on the host."""
+    from synthpop import synth
+    inp = synth.generate_population_inputs(str(tmp_path / "in"), 2_000_000, n_insertions=2000)
+    want = str(tmp_path / "want"); got = str(tmp_path / "got")
+    os.makedirs(want); os.makedirs(got)
+    subprocess.run([oracle_bin, "--quiet", "--seed", "42", "SimulateHaplotypes"] + inp.simulate_argv(want, 6, n_frequent=300), check=True)
+    argv = inp.simulate_argv(got, 6, n_frequent=300)
+    a = sp.Context(0, 42); b = sp.Context(0, 42)
+    a.population_begin(argv, 0, 5); b.population_begin(argv, 6, 11)
+    counts = a.population_local_counts() + b.population_local_counts()
+    oa, ia = a.population_local_lists(6); ob, ib = b.population_local_lists(6)
+    all_off = np.concatenate([oa, ob[1:] + oa[-1]]); all_ids = np.concatenate([ia, ib])
+    a.population_finish(counts, all_off, all_ids, True)
+    b.population_finish(counts, None, None, False)
+    _cmp_dirs(want, got, 6)
+    a.close(); b.close()
