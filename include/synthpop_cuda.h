@@ -53,6 +53,10 @@ int64_t sp_reference_length(const sp_ctx* ctx);
 int sp_set_variants(sp_ctx* ctx, int32_t n, const int8_t* sv_type, const int32_t* position, const int32_t* length,
                     const int64_t* payload_off, const uint8_t* payload_blob, const int8_t* has_payload);
 int sp_set_haplotype_lists(sp_ctx* ctx, int32_t n_haplotypes, const int64_t* list_off, const int32_t* ids);
+/* Read back what the context holds (host copies). Call once with NULL arrays to get the sizes. */
+int sp_get_variants(sp_ctx* ctx, int32_t* n, int64_t* payload_bytes, int8_t* sv_type, int32_t* position, int32_t* length,
+                    int64_t* payload_off, uint8_t* payload_blob);
+int sp_get_haplotype_lists(sp_ctx* ctx, int32_t* n_haplotypes, int64_t* n_ids, int64_t* list_off, int32_t* ids);
 /* SimulateHaplotypes.deserialize(String,String) (src/SimulateHaplotypes.java:1147-1178). */
 int sp_load_population(sp_ctx* ctx, const char* haplotype2variants_file, const char* variants_file);
 
@@ -104,6 +108,9 @@ int sp_simulate_population(sp_ctx* ctx, const sp_population_args* args);
  * then the genotype kernel + collision fixer + carrier counts for haplotypes [first_haplotype..last_haplotype] only
  * (loop A :621-634 is index-addressable: cell (j,i) uses LCG steps S1+2(j*H+i)+1,+2). */
 int sp_population_begin(sp_ctx* ctx, const sp_population_args* args, int32_t first_haplotype, int32_t last_haplotype);
+/* Rows G/C/N once more for haplotypes [first..last] of an already begun population (no file I/O): the fresh lists
+ * stay in HBM and are what the next sp_plan_haplotypes consumes ("genotype sampling + materialisation" per batch). */
+int sp_population_genotypes(sp_ctx* ctx, int32_t first_haplotype, int32_t last_haplotype);
 /* n_variants = lastVariant+1, n_haplotypes = 2*N_INDIVIDUALS, local_entries = list entries of the local shard. */
 int sp_population_info(sp_ctx* ctx, int32_t* n_variants, int32_t* n_haplotypes, int64_t* local_entries,
                        int32_t* n_local_haplotypes_with_collision);
@@ -120,7 +127,8 @@ int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, i
 /* finish: AF := carriers/H and isActive from global_counts (NULL = the local counts are global), then
  * assignInsertionStrings, annotateVariantsWithRepeats, the individual VCFs of the local shard and, when
  * all_off/all_ids (CSR over ALL haplotypes) are given and write_joint_outputs!=0, the joint VCF, haplotype2variants.txt,
- * variants.txt and the histograms. */
+ * variants.txt and the histograms. write_joint_outputs: 0 = individual VCFs only, 1 = joint outputs too,
+ * 2 = write no file at all (benchmarking rows G/C/N/I/R1 without file emission). */
 int sp_population_finish(sp_ctx* ctx, const int32_t* global_counts, const int64_t* all_off, const int32_t* all_ids,
                          int32_t write_joint_outputs);
 

@@ -91,6 +91,7 @@ static void upload_lists(sp_ctx* c) {
     if (!c->h_list_ids.empty())
         SP_CUDA(cudaMemcpyAsync(c->d_list_ids.p, c->h_list_ids.data(), c->h_list_ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
     SP_CUDA(cudaStreamSynchronize(c->stream));
+    c->view_own_lists();
     c->plan_last = -1; c->plan_first = 0;
 }
 
@@ -288,6 +289,29 @@ int sp_set_haplotype_lists(sp_ctx* ctx, int32_t n_haplotypes, const int64_t* lis
     ctx->h_list_off.assign(list_off, list_off + n_haplotypes + 1);
     ctx->h_list_ids.assign(ids, ids + list_off[n_haplotypes]);
     sp::upload_lists(ctx);
+    SP_API_END
+}
+
+int sp_get_variants(sp_ctx* ctx, int32_t* n, int64_t* payload_bytes, int8_t* sv_type, int32_t* position, int32_t* length,
+                    int64_t* payload_off, uint8_t* payload_blob) {
+    SP_API_BEGIN
+    const int32_t nv = ctx->n_variants;
+    if (n) *n = nv;
+    if (payload_bytes) *payload_bytes = (int64_t)ctx->h_payload.size();
+    if (sv_type && nv) memcpy(sv_type, ctx->h_type.data(), nv);
+    if (position && nv) memcpy(position, ctx->h_pos.data(), (size_t)nv * 4);
+    if (length && nv) memcpy(length, ctx->h_len.data(), (size_t)nv * 4);
+    if (payload_off && !ctx->h_payload_off.empty()) memcpy(payload_off, ctx->h_payload_off.data(), ((size_t)nv + 1) * 8);
+    if (payload_blob && !ctx->h_payload.empty()) memcpy(payload_blob, ctx->h_payload.data(), ctx->h_payload.size());
+    SP_API_END
+}
+
+int sp_get_haplotype_lists(sp_ctx* ctx, int32_t* n_haplotypes, int64_t* n_ids, int64_t* list_off, int32_t* ids) {
+    SP_API_BEGIN
+    if (n_haplotypes) *n_haplotypes = ctx->n_haplotypes;
+    if (n_ids) *n_ids = (int64_t)ctx->h_list_ids.size();
+    if (list_off && !ctx->h_list_off.empty()) memcpy(list_off, ctx->h_list_off.data(), ctx->h_list_off.size() * 8);
+    if (ids && !ctx->h_list_ids.empty()) memcpy(ids, ctx->h_list_ids.data(), ctx->h_list_ids.size() * 4);
     SP_API_END
 }
 

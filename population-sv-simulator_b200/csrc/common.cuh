@@ -94,6 +94,15 @@ struct sp_ctx {
     std::vector<int32_t> h_list_ids;
     sp::DevBuf<int64_t> d_list_off;
     sp::DevBuf<int32_t> d_list_ids;
+    // the lists sp_plan_haplotypes consumes: a view over the buffers above (rows [0,n_haplotypes)) or over a fresh
+    // genotype shard still resident on the device (rows [v_h0, v_h0+v_n))
+    const int64_t* v_off_dev = nullptr;
+    const int32_t* v_ids_dev = nullptr;
+    const int64_t* v_off_host = nullptr;
+    int32_t v_h0 = 0, v_n = 0;
+    void view_own_lists() {
+        v_off_dev = d_list_off.p; v_ids_dev = d_list_ids.p; v_off_host = h_list_off.data(); v_h0 = 0; v_n = n_haplotypes;
+    }
 
     // row M plan (current batch of haplotypes [plan_first..plan_last])
     int32_t plan_first = 0, plan_last = -1;

@@ -56,8 +56,8 @@ plan_kernel(const int8_t* __restrict__ type, const int32_t* __restrict__ pos, co
             int64_t* __restrict__ hap_len, int32_t* __restrict__ err) {
     __shared__ int64_t warp_sums[8];
     __shared__ int64_t carry_s;
-    const int hb = blockIdx.x, h = first_hap + hb, tid = threadIdx.x;
-    const int64_t lo = list_off[h], n = list_off[h + 1] - lo;
+    const int hb = blockIdx.x, h = first_hap + hb, tid = threadIdx.x;  // list_off points at the batch's first row
+    const int64_t lo = list_off[hb], n = list_off[hb + 1] - lo;
     const int64_t sb = seg_base[hb];
     const int64_t hdr_off = aux_off[hb], hdr_len = aux_off[hb + 1] - hdr_off;
     if (tid == 0) {
@@ -295,8 +295,8 @@ static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
 void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride) {
     if (c->ref_len <= 0) throw Error(SP_ERR_ARG, "no reference loaded");
-    if (c->n_haplotypes <= 0) throw Error(SP_ERR_ARG, "no haplotype lists loaded");
-    if (first < 0 || last >= c->n_haplotypes || first > last)
+    if (c->v_n <= 0 || !c->v_off_dev) throw Error(SP_ERR_ARG, "no haplotype lists loaded");
+    if (first < c->v_h0 || last >= c->v_h0 + c->v_n || first > last)
         throw Error(SP_ERR_JAVA_EXCEPTION, "ArrayIndexOutOfBoundsException: haplotype range [" + std::to_string(first) + ".." + std::to_string(last) + "]");
     const int nh = last - first + 1;
     c->materialised = false;
@@ -314,8 +314,9 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
     }
     aux_off[nh] = (int64_t)aux.size();
     std::vector<int64_t> seg_base(nh + 1);
-    const int64_t l0 = c->h_list_off[first];
-    for (int i = 0; i <= nh; i++) seg_base[i] = 3 * (c->h_list_off[first + i] - l0) + 5 * (int64_t)i;
+    const int64_t* lo_host = c->v_off_host + (first - c->v_h0);
+    const int64_t l0 = lo_host[0];
+    for (int i = 0; i <= nh; i++) seg_base[i] = 3 * (lo_host[i] - l0) + 5 * (int64_t)i;
     const int64_t nseg = seg_base[nh];
     c->d_aux.reserve(aux.size());
     c->d_aux_off.reserve(nh + 1);
@@ -330,7 +331,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
     SP_CUDA(cudaMemcpyAsync(c->d_seg_base.p, seg_base.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
     SP_CUDA(cudaMemsetAsync(c->d_err.p, 0, 16, st));
     plan_kernel<<<nh, 256, 0, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, c->d_payload_off.p, c->n_variants,
-                                    c->d_list_off.p, c->d_list_ids.p, c->ref_len, first, c->d_aux_off.p,
+                                    c->v_off_dev + (first - c->v_h0), c->v_ids_dev, c->ref_len, first, c->d_aux_off.p,
                                     c->d_seg_base.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_hap_len.p, c->d_err.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());

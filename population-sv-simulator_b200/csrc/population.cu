@@ -120,12 +120,14 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
     for (int32_t v = 0; v < V; v++) P.variants[v].alleleFrequency = ((double)(P.counts_global[v] - 1) + 1.0) / (double)H;
     assign_insertion_strings(P, c->seed);                               // :107-109
     annotate_variants_with_repeats(P, 100);                             // :111
+    const bool skip_individual = (write_joint & 2) != 0;
+    write_joint &= 1;
     if (write_joint) {
         if (!P.have_all_lists) throw Error(SP_ERR_ARG, "the joint outputs need every haplotype's list");
         write_histograms(P, L);
         write_joint_vcf(P, c->h_ref.data(), L);
     }
-    write_individual_vcfs(P, c->h_ref.data(), L, P.h0, P.h1 - 1, P.h_off.data(), P.h_ids.data(), P.h0);  // :1027-1066
+    if (!skip_individual) write_individual_vcfs(P, c->h_ref.data(), L, P.h0, P.h1 - 1, P.h_off.data(), P.h_ids.data(), P.h0);  // :1027-1066
     if (write_joint) write_population_files(P);                        // :114
     // leave the context ready for sp_plan_haplotypes: variant table with payloads + haplotype lists
     publish_variants(c, P);
@@ -146,6 +148,20 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
     if (!c->h_list_ids.empty())
         SP_CUDA(cudaMemcpyAsync(c->d_list_ids.p, c->h_list_ids.data(), c->h_list_ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
     SP_CUDA(cudaStreamSynchronize(c->stream));
+    c->view_own_lists();
+}
+
+// Rows G/C/N again for haplotypes [first..last] with the model, variants and thresholds already resident; the
+// fresh lists stay on the device and become the view sp_plan_haplotypes consumes (no host round trip of the ids).
+void population_genotypes(sp_ctx* c, int32_t first, int32_t last) {
+    if (!c->pop || !c->pop->begun) throw Error(SP_ERR_ARG, "sp_population_begin has not been called");
+    PopulationState& P = *c->pop;
+    if (first < 0 || last >= P.n_haplotypes_total || first > last) throw Error(SP_ERR_ARG, "bad haplotype shard");
+    P.h0 = first; P.h1 = last + 1;
+    run_genotype_and_collisions(c, P);
+    c->v_off_dev = P.d_off2.p; c->v_ids_dev = P.d_ids2.p; c->v_off_host = P.h_off.data();
+    c->v_h0 = first; c->v_n = last - first + 1;
+    c->plan_last = -1; c->plan_first = 0;
 }
 
 }  // namespace sp
@@ -175,6 +191,12 @@ int sp_simulate_population(sp_ctx* ctx, const sp_population_args* args) {
 int sp_population_begin(sp_ctx* ctx, const sp_population_args* args, int32_t first_haplotype, int32_t last_haplotype) {
     SP_API_BEGIN
     sp::population_begin(ctx, args, first_haplotype, last_haplotype);
+    SP_API_END
+}
+
+int sp_population_genotypes(sp_ctx* ctx, int32_t first_haplotype, int32_t last_haplotype) {
+    SP_API_BEGIN
+    sp::population_genotypes(ctx, first_haplotype, last_haplotype);
     SP_API_END
 }
 

@@ -71,6 +71,8 @@ def load() -> C.CDLL:
         "sp_reference_length": (i64, [vp]),
         "sp_set_variants": (C.c_int, [vp, i32, vp, vp, vp, vp, vp, vp]),
         "sp_set_haplotype_lists": (C.c_int, [vp, i32, vp, vp]),
+        "sp_get_variants": (C.c_int, [vp, P(i32), P(i64), vp, vp, vp, vp, vp]),
+        "sp_get_haplotype_lists": (C.c_int, [vp, P(i32), P(i64), vp, vp]),
         "sp_load_population": (C.c_int, [vp, cp, cp]),
         "sp_plan_haplotypes": (C.c_int, [vp, i32, i32, i32, vp, P(i64)]),
         "sp_materialise": (C.c_int, [vp]),
@@ -81,6 +83,7 @@ def load() -> C.CDLL:
         "sp_print_haplotypes": (C.c_int, [vp, i32, i32, cp, cp, cp, cp]),
         "sp_simulate_population": (C.c_int, [vp, P(PopulationArgs)]),
         "sp_population_begin": (C.c_int, [vp, P(PopulationArgs), i32, i32]),
+        "sp_population_genotypes": (C.c_int, [vp, i32, i32]),
         "sp_population_info": (C.c_int, [vp, P(i32), P(i32), P(i64), P(i32)]),
         "sp_population_local_counts": (C.c_int, [vp, vp]),
         "sp_population_counts_device": (C.c_int, [vp, P(vp)]),
@@ -191,6 +194,21 @@ class Context:
             ids = np.zeros(1, dtype=np.int32)
         self._check(self.lib.sp_set_haplotype_lists(self.h, list_off.size - 1, _ptr(list_off), _ptr(ids)))
 
+    def get_variants(self):
+        n, nb = C.c_int32(), C.c_int64()
+        self._check(self.lib.sp_get_variants(self.h, C.byref(n), C.byref(nb), None, None, None, None, None))
+        t = np.zeros(max(n.value, 1), np.int8); p = np.zeros(max(n.value, 1), np.int32); l = np.zeros(max(n.value, 1), np.int32)
+        po = np.zeros(n.value + 1, np.int64); pb = np.zeros(max(nb.value, 1), np.uint8)
+        self._check(self.lib.sp_get_variants(self.h, None, None, _ptr(t), _ptr(p), _ptr(l), _ptr(po), _ptr(pb)))
+        return dict(sv_type=t[: n.value], position=p[: n.value], length=l[: n.value], payload_off=po, payload=pb[: max(nb.value, 1)])
+
+    def get_haplotype_lists(self):
+        h, n = C.c_int32(), C.c_int64()
+        self._check(self.lib.sp_get_haplotype_lists(self.h, C.byref(h), C.byref(n), None, None))
+        off = np.zeros(h.value + 1, np.int64); ids = np.zeros(max(n.value, 1), np.int32)
+        self._check(self.lib.sp_get_haplotype_lists(self.h, None, None, _ptr(off), _ptr(ids)))
+        return off, ids[: n.value]
+
     def deserialize(self, haplotype2variants_file: str, variants_file: str):
         """SimulateHaplotypes.deserialize (src/SimulateHaplotypes.java:1147-1178)."""
         self._check(self.lib.sp_load_population(self.h, haplotype2variants_file.encode(), variants_file.encode()))
@@ -241,6 +259,9 @@ class Context:
     def population_begin(self, argv, first_haplotype: int = 0, last_haplotype: int = -1):
         args = PopulationArgs.from_argv(argv)
         self._check(self.lib.sp_population_begin(self.h, C.byref(args), first_haplotype, last_haplotype))
+
+    def population_genotypes(self, first_haplotype: int, last_haplotype: int):
+        self._check(self.lib.sp_population_genotypes(self.h, first_haplotype, last_haplotype))
 
     def population_info(self):
         nv, nh, ne, nf = C.c_int32(), C.c_int32(), C.c_int64(), C.c_int32()

@@ -84,3 +84,23 @@ def test_sharded_population_matches_single(sp, oracle_bin, tmp_path):
     b.population_finish(counts, None, None, False)
     _cmp_dirs(want, got, 6)
     a.close(); b.close()
+
+
+def test_baseline_config1_chr21_ten_individuals(sp, oracle_bin, tmp_path):
+    """BASELINE.json configs[0]: chr21-sized reference (46 709 983 bp), 10 diploid individuals, 5 000 frequent SVs,
+    30 000 insertion strings — every SimulateHaplotypes output and every haplotype_<i>.fa byte-identical."""
+    from synthpop import synth
+    inp = synth.generate_population_inputs(str(tmp_path / "in"), 46_709_983, n_insertions=30000)
+    want = str(tmp_path / "want"); got = str(tmp_path / "got")
+    os.makedirs(want); os.makedirs(got)
+    subprocess.run([oracle_bin, "--quiet", "--seed", "42", "SimulateHaplotypes"] + inp.simulate_argv(want, 10, n_frequent=5000), check=True)
+    ctx = sp.Context(0, 42)
+    ctx.simulate_haplotypes(inp.simulate_argv(got, 10, n_frequent=5000))
+    _cmp_dirs(want, got, 10)
+    hw = str(tmp_path / "hw"); hg = str(tmp_path / "hg"); os.makedirs(hw); os.makedirs(hg)
+    files = [inp.reference_file, want + "/haplotype2variants.txt", want + "/variants.txt"]
+    subprocess.run([oracle_bin, "--quiet", "PrintHaplotypes", "0", "19"] + files + [hw], check=True)
+    ctx.print_haplotypes(0, 19, *files, hg)
+    for h in range(20):
+        assert open(f"{hw}/haplotype_{h}.fa", "rb").read() == open(f"{hg}/haplotype_{h}.fa", "rb").read(), h
+    ctx.close()
