@@ -304,6 +304,130 @@ collision_fix_kernel(const int8_t* __restrict__ type, const int32_t* __restrict_
     }
 }
 
+// Shared-memory variant of collision_fix_kernel for lists of up to `cap` entries (cap*30+64 bytes of dynamic
+// shared memory): same algorithm, but the heap (ids and a copy of each element's degree, which is valid because the
+// Java only changes an element's degree while it is outside the queue, :678-680), the index map, the adjacency
+// offsets and the per-entry variant fields live on chip, so the serial replay of java.util.PriorityQueue runs at
+// shared-memory latency instead of L2 latency.
+__global__ void __launch_bounds__(32)
+collision_fix_smem_kernel(const int8_t* __restrict__ type, const int32_t* __restrict__ pos, const int32_t* __restrict__ len,
+                          const int64_t* __restrict__ off, int32_t* __restrict__ ids, const int32_t* __restrict__ fdeg,
+                          const int64_t* __restrict__ eoff, int32_t* __restrict__ adj, int32_t cap,
+                          int32_t* __restrict__ cnt2, int32_t* __restrict__ n_fixed) {
+    extern __shared__ int32_t sm[];
+    const int il = blockIdx.x;
+    const int64_t lo = off[il];
+    const int32_t n = (int32_t)(off[il + 1] - lo);
+    const int64_t e0 = eoff[il];
+    const int32_t E = (int32_t)(eoff[il + 1] - e0);
+    if (E == 0) {
+        if (threadIdx.x == 0) cnt2[il] = n;
+        return;
+    }
+    int32_t* s_pos = sm;                  // [cap]
+    int32_t* s_len = s_pos + cap;         // [cap]
+    int32_t* s_adjoff = s_len + cap;      // [cap+1]
+    int32_t* s_qid = s_adjoff + cap + 1;  // [cap] heap: element
+    int32_t* s_qdeg = s_qid + cap;        // [cap] heap: its degree
+    int32_t* s_where = s_qdeg + cap;      // [cap]
+    int32_t* s_deg = s_where + cap;       // [cap]
+    int8_t* s_type = (int8_t*)(s_deg + cap);  // [cap]
+    int8_t* s_removed = s_type + cap;         // [cap]
+    for (int32_t j = threadIdx.x; j < n; j += 32) {
+        const int32_t v = ids[lo + j];
+        s_pos[j] = pos[v]; s_len[j] = len[v]; s_type[j] = type[v];
+        s_deg[j] = 0; s_removed[j] = 0; s_where[j] = -1;
+    }
+    __syncwarp();
+    if (threadIdx.x != 0) return;
+    atomicAdd(n_fixed, 1);
+    int32_t* A = adj + 2 * e0;
+    auto window_end = [&](int32_t j) { return s_pos[j] + (s_type[j] == SP_INS ? 0 : s_len[j] - 1) + COLLISION_DISTANCE; };
+    for (int32_t j = 0; j < n; j++) {
+        if (fdeg[lo + j] == 0) continue;
+        const int lim = window_end(j);
+        for (int32_t k = j + 1; k < n && s_pos[k] <= lim; k++)
+            if (collides_with(s_type[k], s_pos[k], s_len[k], s_type[j], s_pos[j], s_len[j], COLLISION_DISTANCE)) s_deg[k]++;
+    }
+    int32_t acc = 0;
+    for (int32_t j = 0; j < n; j++) {
+        s_adjoff[j] = acc;
+        const int32_t b = s_deg[j];
+        acc += b + fdeg[lo + j];
+        s_where[j] = b;   // temporarily: number of earlier partners
+        s_qid[j] = 0;     // temporarily: fill cursor of the earlier partners
+    }
+    s_adjoff[n] = acc;
+    for (int32_t j = 0; j < n; j++) {
+        if (fdeg[lo + j] == 0) continue;
+        const int lim = window_end(j);
+        int32_t r = 0;
+        for (int32_t k = j + 1; k < n && s_pos[k] <= lim; k++)
+            if (collides_with(s_type[k], s_pos[k], s_len[k], s_type[j], s_pos[j], s_len[j], COLLISION_DISTANCE)) {
+                A[s_adjoff[j] + s_where[j] + r++] = k;
+                A[s_adjoff[k] + s_qid[k]++] = j;
+            }
+    }
+    for (int32_t j = 0; j < n; j++) { s_deg[j] = s_adjoff[j + 1] - s_adjoff[j]; s_where[j] = -1; }
+    int32_t size = 0;
+    auto put = [&](int32_t k, int32_t x, int32_t d) { s_qid[k] = x; s_qdeg[k] = d; s_where[x] = k; };
+    auto siftUp = [&](int32_t k, int32_t x, int32_t d) {
+        while (k > 0) {
+            const int32_t parent = (k - 1) >> 1;
+            const int32_t ed = s_qdeg[parent];
+            if (d >= ed) break;
+            put(k, s_qid[parent], ed);
+            k = parent;
+        }
+        put(k, x, d);
+    };
+    auto siftDown = [&](int32_t k, int32_t x, int32_t d, int32_t m) {
+        const int32_t half = m >> 1;
+        while (k < half) {
+            int32_t child = (k << 1) + 1;
+            const int32_t right = child + 1;
+            int32_t cd = s_qdeg[child];
+            if (right < m) { const int32_t rd = s_qdeg[right]; if (cd > rd) { child = right; cd = rd; } }
+            if (d <= cd) break;
+            put(k, s_qid[child], cd);
+            k = child;
+        }
+        put(k, x, d);
+    };
+    for (int32_t j = 0; j < n; j++) { siftUp(size, j, s_deg[j]); size++; }
+    while (size > 0) {
+        const int32_t x = s_qid[0];
+        const int32_t m = --size;
+        s_where[x] = -1;
+        if (m > 0) siftDown(0, s_qid[m], s_qdeg[m], m);
+        if (s_removed[x]) continue;
+        for (int32_t k = s_adjoff[x]; k < s_adjoff[x + 1]; k++) {
+            const int32_t nb = A[k];
+            if (s_removed[nb]) continue;
+            s_removed[nb] = 1;
+            for (int32_t h = s_adjoff[nb]; h < s_adjoff[nb + 1]; h++) {
+                const int32_t e = A[h];
+                const int32_t i = s_where[e];
+                if (i < 0) continue;            // if (!queue.remove(element)) continue;
+                const int32_t s2 = --size;      // removeAt(i)
+                s_where[e] = -1;
+                if (s2 != i) {
+                    const int32_t moved = s_qid[s2], md = s_qdeg[s2];
+                    siftDown(i, moved, md, s2);
+                    if (s_qid[i] == moved) siftUp(i, moved, md);
+                }
+                const int32_t nd = --s_deg[e];  // element.degree--; queue.add(element);
+                siftUp(size, e, nd);
+                size++;
+            }
+        }
+    }
+    int32_t k = -1;
+    for (int32_t j = 0; j < n; j++)
+        if (!s_removed[j]) ids[lo + (++k)] = ids[lo + j];
+    cnt2[il] = k + 1;
+}
+
 // Survivors -> contiguous CSR (off2) and per-variant carrier counts.
 __global__ void __launch_bounds__(256)
 compact_count_kernel(const int64_t* __restrict__ off, const int32_t* __restrict__ ids, const int32_t* __restrict__ cnt2,
@@ -375,7 +499,20 @@ void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
     P.d_nfixed.reserve(1);
     SP_CUDA(cudaMemsetAsync(P.d_nfixed.p, 0, 4, st));
     SP_CUDA(cudaMemsetAsync(P.d_counts.p, 0, (size_t)std::max(V, 1) * 4, st));
-    if (Hl > 0) {
+    int32_t max_n = 0;
+    for (int32_t i = 0; i < Hl; i++) max_n = std::max<int32_t>(max_n, (int32_t)(off[i + 1] - off[i]));
+    const size_t smem_bytes = (size_t)max_n * 30 + 64;
+    const bool force_global = getenv("SYNTHPOP_FORCE_GLOBAL_COLLISION_FIX") != nullptr;  // test hook
+    if (Hl > 0 && smem_bytes <= 200 * 1024 && !force_global) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            SP_CUDA(cudaFuncSetAttribute(collision_fix_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            attr_set = true;
+        }
+        collision_fix_smem_kernel<<<Hl, 32, smem_bytes, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, P.d_off.p, P.d_ids.p, P.d_fdeg.p,
+                                                              P.d_eoff.p, P.d_adj.p, max_n, P.d_cnt2.p, P.d_nfixed.p);
+        c->launches++;
+    } else if (Hl > 0) {
         collision_fix_kernel<<<Hl, 32, 0, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, P.d_off.p, P.d_ids.p, P.d_fdeg.p, P.d_eoff.p,
                                                 P.d_adj.p, P.d_adj_off.p, P.d_q.p, P.d_where.p, P.d_degree.p, P.d_removed.p,
                                                 P.d_cnt2.p, P.d_nfixed.p);

@@ -104,3 +104,17 @@ def test_baseline_config1_chr21_ten_individuals(sp, oracle_bin, tmp_path):
     for h in range(20):
         assert open(f"{hw}/haplotype_{h}.fa", "rb").read() == open(f"{hg}/haplotype_{h}.fa", "rb").read(), h
     ctx.close()
+
+
+def test_global_memory_collision_fixer_fallback(sp, oracle_bin, tmp_path, monkeypatch):
+    """The fallback used when a haplotype's list does not fit in shared memory gives the same files."""
+    from synthpop import synth
+    monkeypatch.setenv("SYNTHPOP_FORCE_GLOBAL_COLLISION_FIX", "1")
+    inp = synth.generate_population_inputs(str(tmp_path / "in"), 3_000_000, n_insertions=2000, seed=99)
+    want = str(tmp_path / "want"); got = str(tmp_path / "got")
+    os.makedirs(want); os.makedirs(got)
+    subprocess.run([oracle_bin, "--quiet", "--seed", "5", "SimulateHaplotypes"] + inp.simulate_argv(want, 8, n_frequent=600), check=True)
+    ctx = sp.Context(0, 5)
+    ctx.simulate_haplotypes(inp.simulate_argv(got, 8, n_frequent=600))
+    _cmp_dirs(want, got, 8)
+    ctx.close()
