@@ -304,7 +304,7 @@ collision_fix_kernel(const int8_t* __restrict__ type, const int32_t* __restrict_
     }
 }
 
-// Shared-memory variant of collision_fix_kernel for lists of up to `cap` entries (cap*30+64 bytes of dynamic
+// Shared-memory variant of collision_fix_kernel for lists of up to `cap` entries (cap*38+64 bytes of dynamic
 // shared memory): same algorithm, but the heap (ids and a copy of each element's degree, which is valid because the
 // Java only changes an element's degree while it is outside the queue, :678-680), the index map, the adjacency
 // offsets and the per-entry variant fields live on chip, so the serial replay of java.util.PriorityQueue runs at
@@ -331,20 +331,23 @@ collision_fix_smem_kernel(const int8_t* __restrict__ type, const int32_t* __rest
     int32_t* s_qdeg = s_qid + cap;        // [cap] heap: its degree
     int32_t* s_where = s_qdeg + cap;      // [cap]
     int32_t* s_deg = s_where + cap;       // [cap]
-    int8_t* s_type = (int8_t*)(s_deg + cap);  // [cap]
-    int8_t* s_removed = s_type + cap;         // [cap]
+    int32_t* s_id = s_deg + cap;          // [cap] variant ids of the list
+    int32_t* s_fdeg = s_id + cap;         // [cap] forward edge counts
+    int8_t* s_type = (int8_t*)(s_fdeg + cap);  // [cap]
+    int8_t* s_removed = s_type + cap;          // [cap]
     for (int32_t j = threadIdx.x; j < n; j += 32) {
         const int32_t v = ids[lo + j];
+        s_id[j] = v; s_fdeg[j] = fdeg[lo + j];
         s_pos[j] = pos[v]; s_len[j] = len[v]; s_type[j] = type[v];
         s_deg[j] = 0; s_removed[j] = 0; s_where[j] = -1;
     }
     __syncwarp();
-    if (threadIdx.x != 0) return;
-    atomicAdd(n_fixed, 1);
     int32_t* A = adj + 2 * e0;
+    if (threadIdx.x == 0) {
+    atomicAdd(n_fixed, 1);
     auto window_end = [&](int32_t j) { return s_pos[j] + (s_type[j] == SP_INS ? 0 : s_len[j] - 1) + COLLISION_DISTANCE; };
     for (int32_t j = 0; j < n; j++) {
-        if (fdeg[lo + j] == 0) continue;
+        if (s_fdeg[j] == 0) continue;
         const int lim = window_end(j);
         for (int32_t k = j + 1; k < n && s_pos[k] <= lim; k++)
             if (collides_with(s_type[k], s_pos[k], s_len[k], s_type[j], s_pos[j], s_len[j], COLLISION_DISTANCE)) s_deg[k]++;
@@ -353,13 +356,13 @@ collision_fix_smem_kernel(const int8_t* __restrict__ type, const int32_t* __rest
     for (int32_t j = 0; j < n; j++) {
         s_adjoff[j] = acc;
         const int32_t b = s_deg[j];
-        acc += b + fdeg[lo + j];
+        acc += b + s_fdeg[j];
         s_where[j] = b;   // temporarily: number of earlier partners
         s_qid[j] = 0;     // temporarily: fill cursor of the earlier partners
     }
     s_adjoff[n] = acc;
     for (int32_t j = 0; j < n; j++) {
-        if (fdeg[lo + j] == 0) continue;
+        if (s_fdeg[j] == 0) continue;
         const int lim = window_end(j);
         int32_t r = 0;
         for (int32_t k = j + 1; k < n && s_pos[k] <= lim; k++)
@@ -422,10 +425,18 @@ collision_fix_smem_kernel(const int8_t* __restrict__ type, const int32_t* __rest
             }
         }
     }
-    int32_t k = -1;
-    for (int32_t j = 0; j < n; j++)
-        if (!s_removed[j]) ids[lo + (++k)] = ids[lo + j];
-    cnt2[il] = k + 1;
+    }  // lane 0
+    __syncwarp();
+    // survivors keep their order (:684-689): warp-wide ballot compaction back into the list
+    int32_t kept = 0;
+    for (int32_t base = 0; base < n; base += 32) {
+        const int32_t j = base + threadIdx.x;
+        const bool keep = j < n && !s_removed[j];
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (keep) ids[lo + kept + __popc(m & ((1u << threadIdx.x) - 1u))] = s_id[j];
+        kept += __popc(m);
+    }
+    if (threadIdx.x == 0) cnt2[il] = kept;
 }
 
 // Survivors -> contiguous CSR (off2) and per-variant carrier counts.
@@ -501,7 +512,7 @@ void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
     SP_CUDA(cudaMemsetAsync(P.d_counts.p, 0, (size_t)std::max(V, 1) * 4, st));
     int32_t max_n = 0;
     for (int32_t i = 0; i < Hl; i++) max_n = std::max<int32_t>(max_n, (int32_t)(off[i + 1] - off[i]));
-    const size_t smem_bytes = (size_t)max_n * 30 + 64;
+    const size_t smem_bytes = (size_t)max_n * 38 + 64;
     const bool force_global = getenv("SYNTHPOP_FORCE_GLOBAL_COLLISION_FIX") != nullptr;  // test hook
     if (Hl > 0 && smem_bytes <= 200 * 1024 && !force_global) {
         static bool attr_set = false;

@@ -223,3 +223,26 @@ def generate_population_inputs(root: str, length: int, seed: int = GENERATOR_SEE
     return SynthInputs(root=root, reference_file=ref, model_dir=model_dir, repeat_intervals_file=repf,
                        segdups_file=segf, insertions_file=insf, n_insertions=n_insertions,
                        reference_length=length, extra={"bases": bases, "repeat_intervals": rep, "segdups": seg})
+
+
+def write_hmm_model(path: str, seed: int = GENERATOR_SEED, accuracies=range(74, 101), n_states: int = 5,
+                    n_columns: int = 94) -> None:
+    """Synthetic quality-code HMM in the text format set_hmm_model parses (docker/pbsim2.cpp:2583-2647):
+    "<acc> IP <state> <p>", "<acc> EP <state> <94 emission probabilities>", "<acc> TP <state> <p_1..p_n>".
+    (The real P6C4.model is not part of the reference repository.)"""
+    rng = np.random.default_rng(seed + 3)
+    with open(path, "w") as f:
+        for acc in accuracies:
+            ip = rng.dirichlet([2.0] * n_states)
+            for s in range(1, n_states + 1):
+                f.write(f"{acc} IP {s} {ip[s - 1]:.6f}\n")
+            for s in range(1, n_states + 1):
+                centre = min(n_columns - 2, max(2, int(round((acc - 70) * 0.9 + 3 * s))))
+                w = np.zeros(n_columns)
+                lo, hi = max(0, centre - 6), min(n_columns, centre + 7)
+                w[lo:hi] = rng.random(hi - lo) + 0.05
+                w /= w.sum()
+                f.write(f"{acc} EP {s} " + " ".join(f"{x:.6f}" for x in w) + "\n")
+            for s in range(1, n_states + 1):
+                tp = rng.dirichlet([1.5] * n_states)
+                f.write(f"{acc} TP {s} " + " ".join(f"{x:.6f}" for x in tp) + "\n")
