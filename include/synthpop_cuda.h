@@ -132,6 +132,64 @@ int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, i
 int sp_population_finish(sp_ctx* ctx, const int32_t* global_counts, const int64_t* all_off, const int32_t* all_ids,
                          int32_t write_joint_outputs);
 
+/* ---- row P: CCS-like reads (the reference's patched PBSIM2 in model mode, docker/pbsim2.cpp) --------------------- */
+/* How a read finds its rand() draws. The reference has ONE glibc rand() stream per process and the index of a
+ * read's first draw depends on every earlier read (docker/pbsim2.cpp:1641-1711).
+ *   SP_READS_REPLAY ........... the caller supplies the reference's draw stream and the index of each read's first
+ *                               draw (sp_reads_set_replay): output is byte-identical to the reference's file.
+ *   SP_READS_PER_READ_STREAMS . production mode: read r of sequence s draws from its own glibc stream,
+ *                               srand(read_seed(seed, s, r)); same algorithm, same distributions, reads independent
+ *                               of one another (and of how they are sharded over warps or GPUs). */
+enum { SP_READS_PER_READ_STREAMS = 0, SP_READS_REPLAY = 1 };
+
+/* The long options of `pbsim` (docker/pbsim2.cpp:195-213) that model mode uses, as docker/haplotype2reads.sh:32 passes
+ * them. A negative number (NULL string) means "option not given": set_sim_param's default applies (:1047-1107). */
+typedef struct sp_read_args {
+    double depth;           /* --depth            default 20.0 */
+    double length_mean;     /* --length-mean      default 9000 */
+    double length_sd;       /* --length-sd        default 7000 */
+    int64_t length_min;     /* --length-min       default 100 */
+    int64_t length_max;     /* --length-max       default 1000000 */
+    double accuracy_mean;   /* --accuracy-mean    default 0.85; int(x*100)*0.01 is applied as at :1078 */
+    double accuracy_min;    /* --accuracy-min     range-checked, unused in model mode */
+    double accuracy_max;    /* --accuracy-max     range-checked, unused in model mode */
+    int32_t sub_ratio, ins_ratio, del_ratio; /* --difference-ratio sub:ins:del, default 6:54:40 (sub_ratio<0) */
+    const char* hmm_model;  /* --hmm_model        required (selects PROCESS_MODEL, :1175-1180) */
+    const char* prefix;     /* --prefix           default "sd" */
+    const char* id_prefix;  /* --id-prefix        default "S" */
+    uint32_t seed;          /* --seed             (the reference defaults to time(NULL), :191) */
+    int32_t no_error;       /* !=0: docker/pbsim2noError.cpp (prints the error-free oriented substring) */
+    int32_t stream_mode;    /* SP_READS_* */
+} sp_read_args;
+
+/* set_sim_param + set_hmm_model + the lookup tables of simulate_by_model (:1047-1226, :2583-2647, :1455-1637),
+ * built on the host with libm and uploaded as integers. pbsim's own error messages come back via sp_last_error. */
+int sp_reads_configure(sp_ctx* ctx, const sp_read_args* args);
+/* Replay input for the NEXT sp_reads_simulate_* call: draws[k] = k-th value rand() returned after srand(seed) in the
+ * reference run, read_offsets[r] = index of read r's first draw (n_reads entries). */
+int sp_reads_set_replay(sp_ctx* ctx, const int32_t* draws, int64_t n_draws, const int64_t* read_offsets, int64_t n_reads);
+/* simulate_by_model (:1421-1788) + mutate (:2260-2413) for one sequence; reads stay in HBM as the exact records of
+ * <prefix>_%04ld.fastq (">S<ref_num>_<n>Z<seq>\n"). Sources: a planned + materialised haplotype (never leaves the
+ * device), a device buffer of the caller, or host bytes. Outputs (any may be NULL): number of reads simulated,
+ * bytes of the file (dropped reads excluded), reads dropped for containing "NNNNN" (:1711), bases emitted. */
+int sp_reads_simulate_haplotype(sp_ctx* ctx, int32_t h, int64_t ref_num, int64_t* n_reads, int64_t* file_bytes,
+                                int64_t* n_dropped, int64_t* bases);
+int sp_reads_simulate_device(sp_ctx* ctx, const void* device_seq, int64_t seq_len, int64_t ref_num, int64_t* n_reads,
+                             int64_t* file_bytes, int64_t* n_dropped, int64_t* bases);
+int sp_reads_simulate_sequence(sp_ctx* ctx, const uint8_t* seq, int64_t seq_len, int64_t ref_num, int64_t* n_reads,
+                               int64_t* file_bytes, int64_t* n_dropped, int64_t* bases);
+/* D2H of the file bytes of the last simulate call (dropped reads removed on the device first). */
+int sp_reads_copy(sp_ctx* ctx, uint8_t* host_out, int64_t capacity, int64_t* written);
+/* Per-read log of the last simulate call (n_reads entries each, any may be NULL): emitted length, dropped flag,
+ * rand() calls consumed (in replay mode this must equal read_offsets[r+1]-read_offsets[r]). */
+int sp_reads_log(sp_ctx* ctx, int32_t* length, uint8_t* dropped, uint32_t* draws_used);
+/* Device view of the last simulate call: record buffer and the n_reads+1 record offsets (int64) into it. */
+int sp_reads_device(sp_ctx* ctx, void** records, void** record_offsets, void** dropped_flags);
+/* The whole `pbsim` command of docker/haplotype2reads.sh:53: every sequence of the FASTA, output
+ * <prefix>_%04ld.fastq per sequence. (The <prefix>_%04ld.ref copy the reference also leaves is deleted by the
+ * calling script at :54 and is not written.) */
+int sp_simulate_reads(sp_ctx* ctx, const sp_read_args* args, const char* fasta_path);
+
 #ifdef __cplusplus
 }
 #endif

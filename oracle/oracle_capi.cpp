@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY. extern "C" doors into the CPU restatement for ctypes-based tests
 // (known-answer vectors of the JDK/glibc primitives, and in-memory calls of the per-row algorithms).
 #include "simulate_haplotypes.h"
+#include "pbsim_port.h"
 
 extern "C" {
 
@@ -105,6 +106,48 @@ int64_t oracle_build_haplotype(const char* reference, int reference_length, int 
         if ((int64_t)s.size() > out_cap) return -2;
         memcpy(out, s.data(), s.size());
         return (int64_t)s.size();
+    } catch (const std::exception& e) {
+        if (err && err_cap > 0) snprintf(err, err_cap, "%s", e.what());
+        return -1;
+    }
+}
+
+
+// ---- Row P in memory: the pbsim2 restatement on one sequence (a single-record FASTA), srand(seed) at the start.
+// Returns the bytes of <prefix>_0001.fastq written to `out`, -1 on error (message in err), -2 if a capacity is too
+// small. Per-read log arrays (capacity log_cap): first-draw index, emitted length, dropped flag, draws consumed.
+int64_t oracle_pbsim_simulate(const char* hmm_model_file, double depth, double len_mean, double len_sd, long len_min,
+                              long len_max, double accuracy_mean, long sub_ratio, long ins_ratio, long del_ratio,
+                              unsigned seed, const char* id_prefix, int no_error, int per_read_streams, const char* seq,
+                              int64_t seq_len, long ref_num, char* out, int64_t out_cap, int64_t* n_reads,
+                              uint64_t* draw_offset, int64_t* length, uint8_t* dropped, uint64_t* draws_used,
+                              int64_t log_cap, uint64_t* total_draws, char* err, int err_cap) {
+    try {
+        pbsim::Params p;
+        p.depth = depth; p.len_mean = len_mean; p.len_sd = len_sd; p.len_min = len_min; p.len_max = len_max;
+        p.accuracy_mean = accuracy_mean; p.sub_ratio = sub_ratio; p.ins_ratio = ins_ratio; p.del_ratio = del_ratio;
+        p.seed = seed; p.hmm_model_file = hmm_model_file; p.id_prefix = id_prefix ? id_prefix : "S";
+        p.no_error = no_error != 0; p.per_read_streams = per_read_streams != 0;
+        std::vector<pbsim::HmmModel> hmm;
+        pbsim::set_hmm_model(p.hmm_model_file, hmm);
+        pbsim::Tables t;
+        pbsim::build_tables(p, hmm, t);
+        pbsim::GlibcRand rng(p.seed);
+        std::string o;
+        pbsim::ReadLog lg;
+        pbsim::simulate_by_model(p, t, std::string(seq, (size_t)seq_len), ref_num, rng, o, &lg);
+        const int64_t R = (int64_t)lg.length.size();
+        if (n_reads) *n_reads = R;
+        if (total_draws) *total_draws = lg.total_draws;
+        if ((int64_t)o.size() > out_cap || R > log_cap) return -2;
+        memcpy(out, o.data(), o.size());
+        for (int64_t r = 0; r < R; r++) {
+            if (draw_offset) draw_offset[r] = lg.draw_offset[r];
+            if (length) length[r] = lg.length[r];
+            if (dropped) dropped[r] = lg.dropped[r];
+            if (draws_used) draws_used[r] = lg.draws_used[r];
+        }
+        return (int64_t)o.size();
     } catch (const std::exception& e) {
         if (err && err_cap > 0) snprintf(err, err_cap, "%s", e.what());
         return -1;

@@ -316,6 +316,8 @@ void simulate_by_model(const Params& p, const Tables& t, const std::string& ref_
     Mut m;
     char idbuf[256];
     while (len_total < len_quota) {
+        if (p.per_read_streams) rng = GlibcRand(read_seed(p.seed, ref_num, res_num));
+        const uint64_t draws_at_start = rng.count;
         if (log) log->draw_offset.push_back(rng.count);
         long index = rng.next() % t.len_rand_value + 1;
         long len = t.prob2len[index];
@@ -364,7 +366,7 @@ void simulate_by_model(const Params& p, const Tables& t, const std::string& ref_
             out.append(s, (size_t)slen);
             out.push_back('\n');
         }
-        if (log) { log->length.push_back(len); log->dropped.push_back(drop ? 1 : 0); }
+        if (log) { log->length.push_back(len); log->dropped.push_back(drop ? 1 : 0); log->draws_used.push_back(rng.count - draws_at_start); }
     }
     if (log) log->total_draws = rng.count;
 }

@@ -25,7 +25,23 @@ struct Params {  // the options docker/haplotype2reads.sh:32 passes, with pbsim'
     std::string hmm_model_file;
     std::string id_prefix = "S";
     bool no_error = false;  // pbsim2noError.cpp: print mut.seq instead of mut.new_seq
+    // Production mode of the GPU read kernel (NOT a reference behaviour; the reference has one global rand() stream
+    // whose per-read start is data-dependent): every read draws from its own glibc stream, srand(read_seed(seed,
+    // ref_num, read_index)). Everything else is the reference's algorithm, so this mode pins the kernel's
+    // per-read-stream output the same way the default mode pins its replay output.
+    bool per_read_streams = false;
 };
+
+// Seed of read `read_index` (0-based) of sequence `ref_num` (1-based) in per-read-stream mode: splitmix64 finaliser
+// of the three values, mapped to [1, 2^31-2].
+inline unsigned read_seed(unsigned seed, long ref_num, long read_index) {
+    uint64_t z = (uint64_t)seed * 0x9E3779B97F4A7C15ULL + (uint64_t)ref_num * 0xBF58476D1CE4E5B9ULL +
+                 (uint64_t)read_index * 0x94D049BB133111EBULL;
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ULL;
+    z ^= z >> 27; z *= 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    return (unsigned)(1 + z % 2147483646ULL);
+}
 
 struct HmmModel {
     double ip[STATE_MAX + 1];
@@ -65,6 +81,7 @@ struct ReadLog {
     std::vector<uint64_t> draw_offset;  // index of the read's first rand() call
     std::vector<int64_t> length;        // emitted length
     std::vector<uint8_t> dropped;       // 1 = contained "NNNNN", not printed
+    std::vector<uint64_t> draws_used;   // rand() calls the read consumed
     uint64_t total_draws = 0;
 };
 

@@ -29,6 +29,7 @@ int main(int argc, char** argv) {
         else if (s == "--seed") { p.seed = (unsigned)atoi(val()); seed_set = true; }
         else if (s == "--id-prefix") p.id_prefix = val();
         else if (s == "--no-error") p.no_error = true;
+        else if (s == "--per-read-streams") p.per_read_streams = true;
         else if (s == "--log") logfile = val();
         else fasta = s;
     }
@@ -52,8 +53,8 @@ int main(int argc, char** argv) {
             FILE* f = fopen(logfile.c_str(), "w");
             for (size_t k = 0; k < logs.size(); k++)
                 for (size_t r = 0; r < logs[k].draw_offset.size(); r++)
-                    fprintf(f, "%zu\t%zu\t%llu\t%lld\t%d\n", k + 1, r + 1, (unsigned long long)logs[k].draw_offset[r],
-                            (long long)logs[k].length[r], (int)logs[k].dropped[r]);
+                    fprintf(f, "%zu\t%zu\t%llu\t%lld\t%d\t%llu\n", k + 1, r + 1, (unsigned long long)logs[k].draw_offset[r],
+                            (long long)logs[k].length[r], (int)logs[k].dropped[r], (unsigned long long)logs[k].draws_used[r]);
             fclose(f);
         }
     } catch (const std::exception& e) {

@@ -7,6 +7,7 @@ namespace sp {
 void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride);
 void materialise(sp_ctx* c);
 void free_population(sp_ctx* c);
+void free_reads(sp_ctx* c);
 
 std::string java_double_to_string(double d) {
     if (d != d) return "NaN";
@@ -222,6 +223,7 @@ void sp_destroy(sp_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     cudaStream_t s = ctx->own_stream;
     sp::free_population(ctx);
+    sp::free_reads(ctx);
     delete ctx;
     if (s) cudaStreamDestroy(s);
 }

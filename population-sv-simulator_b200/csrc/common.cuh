@@ -12,6 +12,7 @@
 namespace sp {
 
 struct PopulationState;
+struct ReadState;
 
 struct Error : std::runtime_error {
     int code;
@@ -121,4 +122,7 @@ struct sp_ctx {
 
     // rows S1/G/C/N/I/R1/W/Z: one SimulateHaplotypes run
     sp::PopulationState* pop = nullptr;
+
+    // row P: read simulation (pbsim2 model mode)
+    sp::ReadState* reads = nullptr;
 };

@@ -44,6 +44,46 @@ class PopulationArgs(C.Structure):
                    int(a[6]), float(a[7]), int(a[8]), int(a[9]), a[10].encode())
 
 
+READS_PER_READ_STREAMS, READS_REPLAY = 0, 1
+
+
+class ReadArgs(C.Structure):
+    """sp_read_args: the long options of `pbsim` in model mode (docker/pbsim2.cpp:195-213); negative / None = not given."""
+    _fields_ = [("depth", C.c_double), ("length_mean", C.c_double), ("length_sd", C.c_double),
+                ("length_min", C.c_int64), ("length_max", C.c_int64), ("accuracy_mean", C.c_double),
+                ("accuracy_min", C.c_double), ("accuracy_max", C.c_double), ("sub_ratio", C.c_int32),
+                ("ins_ratio", C.c_int32), ("del_ratio", C.c_int32), ("hmm_model", C.c_char_p), ("prefix", C.c_char_p),
+                ("id_prefix", C.c_char_p), ("seed", C.c_uint32), ("no_error", C.c_int32), ("stream_mode", C.c_int32)]
+
+    @classmethod
+    def from_options(cls, argv, no_error=False, stream_mode=READS_PER_READ_STREAMS):
+        """Parse a pbsim command line (list of strings, the trailing FASTA is returned separately)."""
+        a = cls(-1.0, -1.0, -1.0, -1, -1, -1.0, -1.0, -1.0, -1, -1, -1, None, None, None, 0, int(no_error), stream_mode)
+        fasta = None
+        it = iter([str(x) for x in argv])
+        for opt in it:
+            if not opt.startswith("--"):
+                fasta = opt
+                continue
+            val = next(it)
+            if opt == "--depth": a.depth = float(val)
+            elif opt == "--length-mean": a.length_mean = float(val)
+            elif opt == "--length-sd": a.length_sd = float(val)
+            elif opt == "--length-min": a.length_min = int(val)
+            elif opt == "--length-max": a.length_max = int(val)
+            elif opt == "--accuracy-mean": a.accuracy_mean = float(val)
+            elif opt == "--accuracy-min": a.accuracy_min = float(val)
+            elif opt == "--accuracy-max": a.accuracy_max = float(val)
+            elif opt == "--difference-ratio":
+                a.sub_ratio, a.ins_ratio, a.del_ratio = (int(x) for x in val.split(":"))
+            elif opt == "--hmm_model": a.hmm_model = val.encode()
+            elif opt == "--prefix": a.prefix = val.encode()
+            elif opt == "--id-prefix": a.id_prefix = val.encode()
+            elif opt == "--seed": a.seed = int(val) & 0xFFFFFFFF
+            else: raise ValueError(f"pbsim option {opt} is not part of model mode")
+        return a, fasta
+
+
 def _p(dtype):
     return np.ctypeslib.ndpointer(dtype=dtype, flags="C_CONTIGUOUS")
 
@@ -91,6 +131,15 @@ def load() -> C.CDLL:
         "sp_population_pre_collision_lists": (C.c_int, [vp, vp, vp, i64, P(i64)]),
         "sp_population_draw_log": (C.c_int, [vp, P(C.c_uint64), P(i32)]),
         "sp_population_finish": (C.c_int, [vp, vp, vp, vp, i32]),
+        "sp_reads_configure": (C.c_int, [vp, P(ReadArgs)]),
+        "sp_reads_set_replay": (C.c_int, [vp, vp, i64, vp, i64]),
+        "sp_reads_simulate_haplotype": (C.c_int, [vp, i32, i64, P(i64), P(i64), P(i64), P(i64)]),
+        "sp_reads_simulate_device": (C.c_int, [vp, vp, i64, i64, P(i64), P(i64), P(i64), P(i64)]),
+        "sp_reads_simulate_sequence": (C.c_int, [vp, vp, i64, i64, P(i64), P(i64), P(i64), P(i64)]),
+        "sp_reads_copy": (C.c_int, [vp, vp, i64, P(i64)]),
+        "sp_reads_log": (C.c_int, [vp, vp, vp, vp]),
+        "sp_reads_device": (C.c_int, [vp, P(vp), P(vp), P(vp)]),
+        "sp_simulate_reads": (C.c_int, [vp, P(ReadArgs), cp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -306,3 +355,45 @@ class Context:
         if ai is not None and ai.size == 0:
             ai = np.zeros(1, dtype=np.int32)
         self._check(self.lib.sp_population_finish(self.h, _ptr(gc), _ptr(ao), _ptr(ai), int(write_joint_outputs)))
+
+    # ---- row P: reads (pbsim2 model mode) --------------------------------------------------------------------
+    def reads_configure(self, args: "ReadArgs"):
+        self._read_args = args  # keeps the byte strings alive
+        self._check(self.lib.sp_reads_configure(self.h, C.byref(args)))
+
+    def reads_set_replay(self, draws: np.ndarray, read_offsets: np.ndarray):
+        draws = np.ascontiguousarray(draws, dtype=np.int32)
+        off = np.ascontiguousarray(read_offsets, dtype=np.int64)
+        self._check(self.lib.sp_reads_set_replay(self.h, _ptr(draws), draws.size, _ptr(off), off.size))
+
+    def _reads_result(self, fn, *args):
+        n, b, d, e = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        self._check(fn(self.h, *args, C.byref(n), C.byref(b), C.byref(d), C.byref(e)))
+        return dict(n_reads=n.value, file_bytes=b.value, n_dropped=d.value, bases=e.value)
+
+    def reads_simulate_haplotype(self, h: int, ref_num: int = 1):
+        return self._reads_result(self.lib.sp_reads_simulate_haplotype, h, ref_num)
+
+    def reads_simulate_device(self, device_ptr: int, length: int, ref_num: int = 1):
+        return self._reads_result(self.lib.sp_reads_simulate_device, C.c_void_p(device_ptr), length, ref_num)
+
+    def reads_simulate_sequence(self, seq: np.ndarray, ref_num: int = 1):
+        seq = np.ascontiguousarray(seq, dtype=np.uint8)
+        return self._reads_result(self.lib.sp_reads_simulate_sequence, _ptr(seq), seq.size, ref_num)
+
+    def reads_copy(self, capacity: int, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty(max(capacity, 1), dtype=np.uint8)
+        w = C.c_int64()
+        self._check(self.lib.sp_reads_copy(self.h, _ptr(out), out.size, C.byref(w)))
+        return out[:w.value]
+
+    def reads_log(self, n_reads: int):
+        ln = np.zeros(max(n_reads, 1), np.int32); dr = np.zeros(max(n_reads, 1), np.uint8); us = np.zeros(max(n_reads, 1), np.uint32)
+        self._check(self.lib.sp_reads_log(self.h, _ptr(ln), _ptr(dr), _ptr(us)))
+        return ln[:n_reads], dr[:n_reads], us[:n_reads]
+
+    def simulate_reads(self, args: "ReadArgs", fasta_path: str):
+        """The whole `pbsim` command (docker/haplotype2reads.sh:53): writes <prefix>_%04d.fastq per sequence."""
+        self._read_args = args
+        self._check(self.lib.sp_simulate_reads(self.h, C.byref(args), fasta_path.encode()))

@@ -83,3 +83,43 @@ def random_edit_lists(rng, L, n_variants, n_hap, p_carry=0.5, max_len=2000, ins_
     ids = np.concatenate(lists).astype(np.int32) if lists else np.zeros(0, np.int32)
     return dict(ref=ref, sv_type=types, position=pos, length=length, payload_off=payload_off, payload=payload,
                 lists=lists, list_off=list_off, ids=ids)
+
+
+# ---- row P: the pbsim2 restatement ------------------------------------------------------------------------------
+def glibc_rand(lib, seed: int, n: int) -> np.ndarray:
+    """First n values of rand() after srand(seed) (restated glibc TYPE_3 generator, pinned by test_oracle_kat)."""
+    assert 0 <= n < 2**31 - 400, "draw log too long for a test"
+    out = np.empty(max(n, 1), dtype=np.int32)
+    lib.oracle_glibc_rand(C.c_uint(seed), C.c_int(n), _vp(out))
+    return out[:n]
+
+
+def pbsim_simulate(lib, seq: np.ndarray, hmm_model: str, depth, len_mean, len_sd, len_min, len_max, accuracy_mean_cli,
+                   ratio=(6, 54, 40), seed=0, id_prefix="S", no_error=False, per_read_streams=False, ref_num=1):
+    """oracle/pbsim_port.cpp on one in-memory sequence. accuracy_mean_cli is the command-line value (int(x*100)*0.01 is
+    applied here as set_sim_param does). Returns (file bytes, dict of per-read log arrays)."""
+    seq = np.ascontiguousarray(seq, dtype=np.uint8)
+    acc = int(accuracy_mean_cli * 100) * 0.01
+    cap = int(seq.size * depth * 1.3) + (1 << 20)
+    log_cap = int(seq.size * depth / max(1, len_min)) + 1024
+    out = np.empty(cap, dtype=np.uint8)
+    off = np.zeros(log_cap, np.uint64); ln = np.zeros(log_cap, np.int64); dr = np.zeros(log_cap, np.uint8)
+    us = np.zeros(log_cap, np.uint64)
+    n_reads = C.c_int64(); total = C.c_uint64()
+    err = C.create_string_buffer(512)
+    lib.oracle_pbsim_simulate.restype = C.c_int64
+    lib.oracle_pbsim_simulate.argtypes = [C.c_char_p, C.c_double, C.c_double, C.c_double, C.c_long, C.c_long, C.c_double,
+                                          C.c_long, C.c_long, C.c_long, C.c_uint, C.c_char_p, C.c_int, C.c_int, C.c_void_p,
+                                          C.c_int64, C.c_long, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint64), C.c_char_p, C.c_int]
+    n = lib.oracle_pbsim_simulate(hmm_model.encode(), depth, len_mean, len_sd, len_min, len_max, acc, ratio[0], ratio[1],
+                                  ratio[2], seed, id_prefix.encode(), int(no_error), int(per_read_streams), _vp(seq), seq.size,
+                                  ref_num, _vp(out), cap, C.byref(n_reads), _vp(off), _vp(ln), _vp(dr), _vp(us), log_cap,
+                                  C.byref(total), err, 512)
+    if n == -1:
+        raise RuntimeError(err.value.decode())
+    if n < 0:
+        raise RuntimeError("oracle pbsim buffers too small")
+    R = n_reads.value
+    return out[:n].copy(), dict(n_reads=R, draw_offset=off[:R].astype(np.int64), length=ln[:R].copy(), dropped=dr[:R].copy(),
+                                draws_used=us[:R].astype(np.int64), total_draws=int(total.value))

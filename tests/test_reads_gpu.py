@@ -1,0 +1,182 @@
+"""Row P on the GPU: the read kernel against the pbsim2 restatement (oracle/pbsim_port.cpp, itself pinned byte-for-byte
+against the reference's own docker/pbsim2.cpp compiled unmodified, tests/test_pbsim_port.py) and, where the prebuilt
+binary travelled with the snapshot, against that reference binary directly.
+
+Replay mode consumes the reference's draw stream (the values rand() returned after srand(seed)) and the index of
+each read's first draw: the output must be the reference's file, byte for byte. Per-read-stream mode is checked against
+the restatement run with the same per-read seeds."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_helpers as oh
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_BIN = os.path.join(ROOT, "oracle", "_ref")
+
+CCS = dict(depth=5.0, len_mean=15000.0, len_sd=2000.0, len_min=5000, len_max=30000, accuracy_mean_cli=0.995, ratio=(6, 50, 54))
+
+
+def _cli(p, seed, model, prefix=None):
+    a = ["--depth", str(p["depth"]), "--length-mean", str(p["len_mean"]), "--length-sd", str(p["len_sd"]),
+         "--length-min", str(p["len_min"]), "--length-max", str(p["len_max"]), "--accuracy-mean", str(p["accuracy_mean_cli"]),
+         "--accuracy-min", "0.99", "--accuracy-max", "1.0", "--difference-ratio", ":".join(str(x) for x in p["ratio"]),
+         "--hmm_model", model, "--seed", str(seed)]
+    if prefix:
+        a += ["--prefix", prefix]
+    return a
+
+
+def _model(tmp_path, kind):
+    from synthpop import synth
+    mf = str(tmp_path / f"{kind}.model")
+    if kind == "empty":
+        open(mf, "w").close()
+    elif kind == "hmm":
+        synth.write_hmm_model(mf)
+    elif kind == "hmm_partial":
+        synth.write_hmm_model(mf, accuracies=range(90, 99))
+    elif kind == "hmm_sparse":  # state indices 3, 7, 20, 41: exercises the renumbering of visited states
+        _states_model(mf, (3, 7, 20, 41))
+    elif kind == "hmm_wide":    # 20 states: beyond the nibble maps, serial tile path
+        _states_model(mf, tuple(range(1, 21)))
+    return mf
+
+
+def _states_model(path, states):
+    """HMM over the given state indices; emission windows stay below Q30 so that the deletion rejection loop
+    (acceptance 10^(-q/10), docker/pbsim2.cpp:2284-2292) keeps the draw log of a test small."""
+    rng = np.random.default_rng(5)
+    with open(path, "w") as f:
+        for acc in range(74, 101):
+            ip = rng.dirichlet([2.0] * len(states))
+            for s, p in zip(states, ip):
+                f.write(f"{acc} IP {s} {p:.6f}\n")
+            for s in states:
+                w = np.zeros(94); c = int(rng.integers(5, 22)); w[c:c + 8] = rng.random(8) + 0.05; w /= w.sum()
+                f.write(f"{acc} EP {s} " + " ".join(f"{x:.6f}" for x in w) + "\n")
+            for s in states:
+                row = np.zeros(max(states))
+                row[[t - 1 for t in states]] = rng.dirichlet([1.5] * len(states))
+                f.write(f"{acc} TP {s} " + " ".join(f"{x:.6f}" for x in row) + "\n")
+
+
+def _haplotype(L, seed=3):
+    from synthpop import synth
+    bases, _, _ = synth.random_reference(L, seed)  # N runs at both ends and in a centromere block, soft-masked repeats
+    return bases
+
+
+def _configure(sp, ctx, p, seed, model, no_error, mode):
+    args, _ = sp.ReadArgs.from_options(_cli(p, seed, model), no_error=no_error, stream_mode=mode)
+    ctx.reads_configure(args)
+
+
+@pytest.mark.parametrize("kind,no_error,seed,params", [
+    ("empty", False, 42, CCS), ("hmm", False, 42, CCS), ("hmm", True, 1, CCS), ("hmm_partial", False, 99, CCS),
+    ("empty", True, 7, CCS), ("hmm_sparse", False, 5, CCS), ("hmm_wide", False, 6, dict(CCS, depth=2.0)),
+    ("empty", False, 8, dict(depth=3.0, len_mean=9000.0, len_sd=7000.0, len_min=100, len_max=1000000, accuracy_mean_cli=0.85, ratio=(6, 54, 40))),
+    ("hmm", False, 3, dict(CCS, len_mean=7000.0, len_sd=0.0, accuracy_mean_cli=0.9, depth=4.0)),
+])
+def test_replay_is_byte_identical_to_the_reference(sp, oracle_lib, tmp_path, kind, no_error, seed, params):
+    L = 600_000
+    hap = _haplotype(L)
+    model = _model(tmp_path, kind)
+    want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=seed, no_error=no_error, **params)
+    assert log["n_reads"] > 20 and len(want) > 500_000
+    exe = os.path.join(REF_BIN, "pbsim2noError" if no_error else "pbsim2")
+    if os.path.exists(exe):  # the reference itself, compiled from its own sources (oracle/Makefile)
+        fa = str(tmp_path / "hap.fa")
+        with open(fa, "wb") as f:
+            f.write(b">chr1_0\n" + hap.tobytes() + b"\n")
+        subprocess.run([exe] + _cli(params, seed, model, str(tmp_path / "ref")) + [fa], check=True, stderr=subprocess.DEVNULL)
+        assert open(tmp_path / "ref_0001.fastq", "rb").read() == want.tobytes()
+    draws = oh.glibc_rand(oracle_lib, seed, log["total_draws"])
+    with sp.Context(0, 42) as ctx:
+        _configure(sp, ctx, params, seed, model, no_error, sp.READS_REPLAY)
+        ctx.reads_set_replay(draws, log["draw_offset"])
+        res = ctx.reads_simulate_sequence(hap)
+        assert res["n_reads"] == log["n_reads"]
+        assert res["n_dropped"] == int(log["dropped"].sum())
+        got = ctx.reads_copy(res["file_bytes"])
+        ln, dr, used = ctx.reads_log(res["n_reads"])
+    assert np.array_equal(ln, log["length"]) and np.array_equal(dr, log["dropped"])
+    assert np.array_equal(used.astype(np.int64), log["draws_used"])
+    assert got.size == want.size and np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("kind,no_error,seed", [("empty", False, 11), ("hmm", False, 12), ("hmm", True, 13), ("hmm_sparse", False, 14)])
+def test_per_read_streams_match_the_restatement(sp, oracle_lib, tmp_path, kind, no_error, seed):
+    hap = _haplotype(500_000, seed=9)
+    model = _model(tmp_path, kind)
+    want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=seed, no_error=no_error, per_read_streams=True, ref_num=3, **CCS)
+    with sp.Context(0, 42) as ctx:
+        _configure(sp, ctx, CCS, seed, model, no_error, sp.READS_PER_READ_STREAMS)
+        res = ctx.reads_simulate_sequence(hap, ref_num=3)
+        got = ctx.reads_copy(res["file_bytes"])
+        ln, dr, used = ctx.reads_log(res["n_reads"])
+    assert res["n_reads"] == log["n_reads"] and res["bases"] == int(log["length"].sum())
+    assert np.array_equal(used.astype(np.int64), log["draws_used"])
+    assert np.array_equal(dr, log["dropped"]) and dr.sum() > 0  # reads over the N runs are dropped (:1711)
+    assert np.array_equal(got, want)
+
+
+def test_reads_from_a_materialised_haplotype_never_leave_the_device(sp, oracle_lib, tmp_path):
+    """PrintHaplotypes -> pbsim without the .fa file: plan + materialise + read kernel on the resident haplotype."""
+    rng = np.random.default_rng(77)
+    case = oh.random_edit_lists(rng, 400_000, 200, 2, max_len=3000)
+    model = _model(tmp_path, "hmm")
+    p = dict(CCS, depth=3.0)
+    with sp.Context(0, 42) as ctx:
+        ctx.set_reference(case["ref"])
+        ctx.set_variants(case["sv_type"], case["position"], case["length"], case["payload_off"], case["payload"])
+        ctx.set_haplotype_lists(case["list_off"], case["ids"])
+        ctx.plan_haplotypes(0, 1, False)
+        ctx.materialise()
+        _configure(sp, ctx, p, 21, model, False, sp.READS_PER_READ_STREAMS)
+        for h in range(2):
+            hap = oh.build_haplotype(oracle_lib, case["ref"], case["sv_type"], case["position"], case["length"],
+                                     case["payload_off"], case["payload"], None, case["lists"][h])
+            want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)
+            res = ctx.reads_simulate_haplotype(h, ref_num=h + 1)
+            got = ctx.reads_copy(res["file_bytes"])
+            assert res["n_reads"] == log["n_reads"] and np.array_equal(got, want), h
+
+
+def test_pbsim_command_writes_the_reference_file_layout(sp, oracle_lib, tmp_path):
+    """sp_simulate_reads = the `pbsim` command of docker/haplotype2reads.sh:53 on a two-sequence FASTA."""
+    a, b = _haplotype(300_000, seed=1), _haplotype(200_000, seed=2)
+    fa = str(tmp_path / "two.fa")
+    with open(fa, "wb") as f:
+        f.write(b">first\n" + a.tobytes() + b"\n>second\n")
+        for i in range(0, b.size, 70):  # line-wrapped record
+            f.write(b[i:i + 70].tobytes() + b"\n")
+    model = _model(tmp_path, "hmm")
+    p = dict(CCS, depth=4.0)
+    with sp.Context(0, 42) as ctx:
+        args, _ = sp.ReadArgs.from_options(_cli(p, 5, model, str(tmp_path / "reads_7")))
+        ctx.simulate_reads(args, fa)
+    for k, seq in enumerate((a, b)):
+        want, _ = oh.pbsim_simulate(oracle_lib, seq, model, seed=5, per_read_streams=True, ref_num=k + 1, **p)
+        assert open(tmp_path / f"reads_7_{k + 1:04d}.fastq", "rb").read() == want.tobytes()
+
+
+def test_pbsim_argument_errors(sp, tmp_path):
+    with sp.Context(0, 42) as ctx:
+        args, _ = sp.ReadArgs.from_options(["--depth", "5"])
+        with pytest.raises(sp.SynthpopError, match="hmm_model"):
+            ctx.reads_configure(args)
+        mf = str(tmp_path / "m"); open(mf, "w").close()
+        args, _ = sp.ReadArgs.from_options(["--length-min", "9000", "--length-max", "100", "--hmm_model", mf])
+        with pytest.raises(sp.SynthpopError, match="greater than max"):
+            ctx.reads_configure(args)
+        args, _ = sp.ReadArgs.from_options(["--hmm_model", str(tmp_path / "missing")])
+        with pytest.raises(sp.SynthpopError, match="Cannot open file"):
+            ctx.reads_configure(args)
+        args, _ = sp.ReadArgs.from_options(["--hmm_model", mf, "--depth", "2"])
+        ctx.reads_configure(args)
+        with pytest.raises(sp.SynthpopError, match="too short"):
+            ctx.reads_simulate_sequence(np.frombuffer(b"ACGT" * 10, np.uint8))
