@@ -68,6 +68,68 @@ def random_reference(L: int, seed: int = 20261104) -> np.ndarray:
     return np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=L, dtype=np.uint8)].copy()
 
 
+CCS_CLI = ["--length-min", "5000", "--length-max", "30000", "--accuracy-min", "0.99", "--accuracy-max", "1.0",
+           "--difference-ratio", "6:50:54", "--length-mean", "15000", "--length-sd", "2000", "--accuracy-mean", "0.995"]
+READ_ALGO_BYTES_PER_BASE = 2.0  # 1 B of haplotype read + 1 B of read written per emitted base
+
+
+def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch):
+    """BASELINE configs[3] on this GPU's shard: pbsim2-model CCS reads at `depth`x over `n_haps` chr1-sized haplotypes that
+    were materialised on the device and never leave it. Returns the `reads` object of the bench line."""
+    model = os.path.join(work, "P6C4_synthetic.model")
+    synth.write_hmm_model(model)
+    args, _ = splib.ReadArgs.from_options(CCS_CLI + ["--depth", str(depth), "--hmm_model", model, "--seed", "42"],
+                                          stream_mode=splib.READS_PER_READ_STREAMS)
+    ctx.reads_configure(args)
+    ctx.population_genotypes(first_hap, first_hap + n_haps - 1)   # rows G/C/N for these haplotypes
+    ctx.plan_haplotypes(first_hap, first_hap + n_haps - 1, False)
+    ctx.materialise()
+    ctx.synchronize()
+    l0 = ctx.kernel_launches
+    # warm-up on the first haplotype (allocations, table upload), then the timed pass over all of them
+    ctx.reads_simulate_haplotype(first_hap, 1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    bases = reads = dropped = 0
+    k_ms = p_ms = 0.0
+    for h in range(first_hap, first_hap + n_haps):
+        r = ctx.reads_simulate_haplotype(h, h + 1)
+        tm = ctx.reads_timing()
+        bases += r["bases"]; reads += r["n_reads"]; dropped += r["n_dropped"]
+        k_ms += tm["kernel_ms"]; p_ms += tm["plan_ms"]
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    achieved = READ_ALGO_BYTES_PER_BASE * bases / (k_ms / 1e3) / 1e9
+    return {"metric": "CCS read Gbp/s", "value": bases / dt / 1e9, "unit": "Gbp/s",
+            "workload": f"pbsim2 model mode, {depth}x over {n_haps} materialised chr1-sized haplotypes, length 15000+-2000 in [5000,30000], "
+                        "accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model, per-read glibc streams",
+            "reads": reads, "dropped_NNNNN": dropped, "bases": bases, "wall_s": dt, "kernel_ms": k_ms, "host_plan_ms": p_ms,
+            "kernel_gbp_s": bases / (k_ms / 1e3) / 1e9, "gpu_launches": ctx.kernel_launches - l0,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE}}
+
+
+def reads_cpu_baseline(synth, work, L=1_500_000, depth=30):
+    """The reference's own docker/pbsim2.cpp (compiled unmodified into oracle/_ref/pbsim2) on a bounded sample: one core,
+    as the reference runs it (one pbsim process per haplotype)."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "pbsim2")
+    if not os.path.exists(exe):
+        return None
+    bases, _, _ = synth.random_reference(L, 7)
+    fa = os.path.join(work, "cpu_reads.fa")
+    synth.write_fasta(fa, ">chr1_0", bases)
+    model = os.path.join(work, "P6C4_synthetic.model")
+    if not os.path.exists(model):
+        synth.write_hmm_model(model)
+    t0 = time.perf_counter()
+    subprocess.run([exe] + CCS_CLI + ["--depth", str(depth), "--hmm_model", model, "--seed", "42", "--prefix",
+                                      os.path.join(work, "cpu_reads"), fa], check=True, stderr=subprocess.DEVNULL)
+    dt = time.perf_counter() - t0
+    n = depth * L
+    return {"value": n / dt / 1e9, "unit": "Gbp/s", "cores": 1, "kind": "reference",
+            "sample": f"oracle/_ref/pbsim2 (the reference's docker/pbsim2.cpp, unmodified), {depth}x over a {L} bp sequence in {dt:.1f} s"}
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
 
@@ -129,6 +191,8 @@ def main():
     ap.add_argument("--length", type=int, default=CHR1)
     ap.add_argument("--e2e-haplotypes", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--read-haplotypes", type=int, default=2, help="haplotypes of the CCS read leg (0 = skip)")
+    ap.add_argument("--read-depth", type=int, default=30)
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -254,6 +318,20 @@ def main():
     pop["lists"] = [pop["ids"][pop["list_off"][h]:pop["list_off"][h + 1]] for h in range(64)]
     ref = inp.extra["bases"]
 
+    # CCS read leg (row P): every rank simulates reads over its own haplotypes; no collective
+    reads_obj = None
+    if args.read_haplotypes > 0:
+        peak, peak_kind = measured_peak_gbs()
+        a0 = (rank * args.read_haplotypes) % (N_HAPLOTYPES - args.read_haplotypes)
+        reads_obj = reads_leg(ctx, splib, synth, work, a0, args.read_haplotypes, args.read_depth, peak, torch)
+        if dist is not None:
+            tr = torch.tensor([reads_obj["wall_s"], reads_obj["kernel_ms"]], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tr, op=dist.ReduceOp.MAX)
+            tb = torch.tensor([float(reads_obj["bases"])], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tb, op=dist.ReduceOp.SUM)
+            reads_obj["value"] = float(tb[0]) / float(tr[0]) / 1e9
+            reads_obj["wall_s"] = float(tr[0])
+
     # e2e: the reference-facing call with HOST buffers — reference + variant table + lists H2D, plan, materialise, D2H
     ne = args.e2e_haplotypes
     host_out = torch.empty(int((L + (4 << 20)) * max(ne, 1)) if ne > 0 else 16, dtype=torch.uint8, pin_memory=True)
@@ -298,7 +376,13 @@ def main():
                 "e2e": {"value": float(e2e_val[0]), "unit": "Gbp/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "haplotypes_per_call": ne},
                 "clocks": sampler.summary(), "wall_s_timed_region": t_wall}
+        if reads_obj is not None:
+            line["reads"] = reads_obj
         if world == 1 and not args.no_cpu_baseline:
+            if reads_obj is not None:
+                rb = reads_cpu_baseline(synth, work)
+                if rb is not None:
+                    reads_obj["cpu_baseline"] = rb
             v, n, dt = cpu_baseline_sample(ref, pop)
             line["cpu_baseline"] = {"value": v, "unit": "Gbp/s", "cores": 1, "kind": "port",
                                     "sample": f"{n} chr1-sized haplotypes in {dt:.1f} s (CPU restatement of buildHaplotypes, 1 thread)"}

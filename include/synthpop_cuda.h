@@ -183,6 +183,9 @@ int sp_reads_copy(sp_ctx* ctx, uint8_t* host_out, int64_t capacity, int64_t* wri
 /* Per-read log of the last simulate call (n_reads entries each, any may be NULL): emitted length, dropped flag,
  * rand() calls consumed (in replay mode this must equal read_offsets[r+1]-read_offsets[r]). */
 int sp_reads_log(sp_ctx* ctx, int32_t* length, uint8_t* dropped, uint32_t* draws_used);
+/* Timing of the last simulate call: host milliseconds of the per-read plan (:1641-1655 for every read) and device
+ * milliseconds of the read kernel (CUDA events on the launching stream). */
+int sp_reads_timing(sp_ctx* ctx, double* plan_ms, double* kernel_ms);
 /* Device view of the last simulate call: record buffer and the n_reads+1 record offsets (int64) into it. */
 int sp_reads_device(sp_ctx* ctx, void** records, void** record_offsets, void** dropped_flags);
 /* The whole `pbsim` command of docker/haplotype2reads.sh:53: every sequence of the FASTA, output

@@ -337,6 +337,7 @@ void reads_configure(sp_ctx* c, const sp_read_args* a) {
 }
 
 void free_reads(sp_ctx* c) {
+    if (c->reads && c->reads->ev0) { cudaEventDestroy(c->reads->ev0); cudaEventDestroy(c->reads->ev1); }
     delete c->reads;
     c->reads = nullptr;
 }

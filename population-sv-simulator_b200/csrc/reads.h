@@ -84,6 +84,10 @@ struct ReadState {
     DevBuf<int64_t> d_rec_off, d_replay_off, d_koff;
     DevBuf<uint32_t> d_used;
     DevBuf<int32_t> d_ctr;  // [0] work counter, [1] error code, [2] error read
+    // device time of the last read kernel (CUDA events on the launching stream) and host time of the per-read plan
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float kernel_ms = 0.f;
+    double plan_ms = 0.0;
 };
 
 void reads_configure(sp_ctx* c, const sp_read_args* a);

@@ -139,6 +139,7 @@ def load() -> C.CDLL:
         "sp_reads_copy": (C.c_int, [vp, vp, i64, P(i64)]),
         "sp_reads_log": (C.c_int, [vp, vp, vp, vp]),
         "sp_reads_device": (C.c_int, [vp, P(vp), P(vp), P(vp)]),
+        "sp_reads_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double)]),
         "sp_simulate_reads": (C.c_int, [vp, P(ReadArgs), cp]),
     }
     for name, (res, args) in sig.items():
@@ -392,6 +393,11 @@ class Context:
         ln = np.zeros(max(n_reads, 1), np.int32); dr = np.zeros(max(n_reads, 1), np.uint8); us = np.zeros(max(n_reads, 1), np.uint32)
         self._check(self.lib.sp_reads_log(self.h, _ptr(ln), _ptr(dr), _ptr(us)))
         return ln[:n_reads], dr[:n_reads], us[:n_reads]
+
+    def reads_timing(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(self.lib.sp_reads_timing(self.h, C.byref(a), C.byref(b)))
+        return dict(plan_ms=a.value, kernel_ms=b.value)
 
     def simulate_reads(self, args: "ReadArgs", fasta_path: str):
         """The whole `pbsim` command (docker/haplotype2reads.sh:53): writes <prefix>_%04d.fastq per sequence."""
