@@ -193,6 +193,35 @@ int sp_reads_device(sp_ctx* ctx, void** records, void** record_offsets, void** d
  * calling script at :54 and is not written.) */
 int sp_simulate_reads(sp_ctx* ctx, const sp_read_args* args, const char* fasta_path);
 
+/* ---- row D: SampleReadsFromLengthBins ------------------------------------------------------------------------------ */
+/* Positional argv of SampleReadsFromLengthBins.main (src/SampleReadsFromLengthBins.java:20-30). args[0..4] (the two
+ * normal distributions and the left weight) only feed buildCumulativeBimodal (:87-102), which needs commons-math3's
+ * NormalDistribution; the host computes that table (N_BINS doubles, cumulative) and passes it, so that the native side
+ * never re-implements erf. N_BINS = (MAX_READ_LENGTH+BIN_LENGTH-1)/BIN_LENGTH (:36). */
+typedef struct sp_length_bin_args {
+    const double* cumulative;               /* cumulativeBimodal[N_BINS] (:47) */
+    int32_t bin_length;                     /* args[5] */
+    int32_t max_read_length;                /* args[6] */
+    const char* bins_prefix;                /* args[7]: files <prefix><i>.bin, 4-line FASTQ records */
+    int64_t genome_length_each_haplotype;   /* args[8] */
+    double target_coverage_each_haplotype;  /* args[9] */
+    const char* output_fastq_file;          /* args[10]; <file>.histogram is written next to it (:78-80) */
+} sp_length_bin_args;
+/* The whole main (:19-81) with `new Random(seed)` of the context: returns 0, or SP_ERR_COVERAGE (= 3, the reference's
+ * System.exit(3), :64-67) when N_BINS*10 consecutive attempts hit bins that ran dry. */
+int sp_sample_reads_from_bins(sp_ctx* ctx, const sp_length_bin_args* args);
+/* The same in steps, with the bins resident in HBM. load: reads <prefix><i>.bin, i in [0,n_bins). set: the bin files
+ * back to back in host memory (bin_off: n_bins+1 byte offsets). */
+int sp_length_bins_load(sp_ctx* ctx, const char* bins_prefix, int32_t n_bins);
+int sp_length_bins_set(sp_ctx* ctx, int32_t n_bins, const uint8_t* blob, const int64_t* bin_off);
+/* The sampling loop (:53-76) until `coverage >= target_coverage_bp`; the FASTQ bytes stay on the device. Outputs (any may
+ * be NULL): reads written, bytes of the FASTQ, nextDouble() draws consumed, sequence bases, histogram[n_bins]. */
+int sp_length_bins_sample(sp_ctx* ctx, const double* cumulative, int32_t n_bins, int64_t target_coverage_bp, int64_t* n_reads,
+                          int64_t* fastq_bytes, int64_t* attempts, int64_t* bases, int32_t* histogram);
+int sp_length_bins_copy(sp_ctx* ctx, uint8_t* host_out, int64_t capacity, int64_t* written);
+/* Device milliseconds of the last sample call: draw/rank/scan/emit kernels, and the tiled gather-copy. */
+int sp_length_bins_timing(sp_ctx* ctx, double* sample_ms, double* copy_ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,6 +8,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
 void materialise(sp_ctx* c);
 void free_population(sp_ctx* c);
 void free_reads(sp_ctx* c);
+void free_length_bins(sp_ctx* c);
 
 std::string java_double_to_string(double d) {
     if (d != d) return "NaN";
@@ -224,6 +225,7 @@ void sp_destroy(sp_ctx* ctx) {
     cudaStream_t s = ctx->own_stream;
     sp::free_population(ctx);
     sp::free_reads(ctx);
+    sp::free_length_bins(ctx);
     delete ctx;
     if (s) cudaStreamDestroy(s);
 }

@@ -13,6 +13,7 @@ namespace sp {
 
 struct PopulationState;
 struct ReadState;
+struct LengthBinState;
 
 struct Error : std::runtime_error {
     int code;
@@ -125,4 +126,7 @@ struct sp_ctx {
 
     // row P: read simulation (pbsim2 model mode)
     sp::ReadState* reads = nullptr;
+
+    // row D: SampleReadsFromLengthBins
+    sp::LengthBinState* bins = nullptr;
 };

@@ -375,4 +375,21 @@ void materialise(sp_ctx* c) {
     c->materialised = true;
 }
 
+// The tiled copy on caller-built segment tables (row D reuses it: records of the length-bin blob -> FASTQ bytes).
+// n_slots slots of `stride` bytes; slot s owns segments [seg_base[s], seg_base[s+1]) laid out as plan_kernel does:
+// ascending seg_dst, then a PAD segment at the slot's total length and a sentinel with dst = INT64_MAX.
+void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
+                       const int64_t* seg_src, const int64_t* seg_base, int32_t* tile_first, uint8_t* out, int64_t stride,
+                       int n_slots) {
+    const int64_t tiles_per_slot = stride / TILE_BYTES;
+    const int64_t ntiles = tiles_per_slot * n_slots;
+    if (ntiles <= 0) return;
+    if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "tiled copy: too many tiles");
+    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, c->stream>>>(seg_dst, seg_base, n_slots, tiles_per_slot, tile_first);
+    materialise_kernel<<<(unsigned)ntiles, 256, 0, c->stream>>>(src, payload, aux, seg_dst, seg_src, seg_base, tile_first, out,
+                                                                stride, tiles_per_slot, n_slots);
+    c->launches += 2;
+    SP_CUDA(cudaGetLastError());
+}
+
 }  // namespace sp

@@ -47,6 +47,13 @@ class PopulationArgs(C.Structure):
 READS_PER_READ_STREAMS, READS_REPLAY = 0, 1
 
 
+class LengthBinArgs(C.Structure):
+    """sp_length_bin_args: argv[5..10] of SampleReadsFromLengthBins.main + the cumulative table (src/SampleReadsFromLengthBins.java:20-47)."""
+    _fields_ = [("cumulative", C.POINTER(C.c_double)), ("bin_length", C.c_int32), ("max_read_length", C.c_int32),
+                ("bins_prefix", C.c_char_p), ("genome_length_each_haplotype", C.c_int64),
+                ("target_coverage_each_haplotype", C.c_double), ("output_fastq_file", C.c_char_p)]
+
+
 class ReadArgs(C.Structure):
     """sp_read_args: the long options of `pbsim` in model mode (docker/pbsim2.cpp:195-213); negative / None = not given."""
     _fields_ = [("depth", C.c_double), ("length_mean", C.c_double), ("length_sd", C.c_double),
@@ -141,6 +148,12 @@ def load() -> C.CDLL:
         "sp_reads_device": (C.c_int, [vp, P(vp), P(vp), P(vp)]),
         "sp_reads_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double)]),
         "sp_simulate_reads": (C.c_int, [vp, P(ReadArgs), cp]),
+        "sp_sample_reads_from_bins": (C.c_int, [vp, P(LengthBinArgs)]),
+        "sp_length_bins_load": (C.c_int, [vp, cp, i32]),
+        "sp_length_bins_set": (C.c_int, [vp, i32, vp, vp]),
+        "sp_length_bins_sample": (C.c_int, [vp, vp, i32, i64, P(i64), P(i64), P(i64), P(i64), vp]),
+        "sp_length_bins_copy": (C.c_int, [vp, vp, i64, P(i64)]),
+        "sp_length_bins_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -403,3 +416,49 @@ class Context:
         """The whole `pbsim` command (docker/haplotype2reads.sh:53): writes <prefix>_%04d.fastq per sequence."""
         self._read_args = args
         self._check(self.lib.sp_simulate_reads(self.h, C.byref(args), fasta_path.encode()))
+
+    # ---- row D: SampleReadsFromLengthBins -------------------------------------------------------------------------
+    def sample_reads_from_length_bins(self, argv, cumulative: np.ndarray):
+        """SampleReadsFromLengthBins.main(args) (src/SampleReadsFromLengthBins.java:19-81): same positional argv; the
+        cumulative bimodal table (buildCumulativeBimodal :87-102) is computed by the caller. Raises SynthpopError with
+        code 3 where the reference calls System.exit(3)."""
+        a = [str(x) for x in argv]
+        if len(a) < 11:
+            raise IndexError("SampleReadsFromLengthBins takes 11 positional arguments")
+        cum = np.ascontiguousarray(cumulative, dtype=np.float64)
+        args = LengthBinArgs(cum.ctypes.data_as(C.POINTER(C.c_double)), int(a[5]), int(a[6]), a[7].encode(), int(a[8]),
+                             float(a[9]), a[10].encode())
+        n_bins = (int(a[6]) + int(a[5]) - 1) // int(a[5])
+        if cum.size != n_bins:
+            raise ValueError(f"cumulative table must have N_BINS={n_bins} entries")
+        self._check(self.lib.sp_sample_reads_from_bins(self.h, C.byref(args)))
+
+    def length_bins_load(self, bins_prefix: str, n_bins: int):
+        self._check(self.lib.sp_length_bins_load(self.h, bins_prefix.encode(), n_bins))
+
+    def length_bins_set(self, blob: np.ndarray, bin_off: np.ndarray):
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        off = np.ascontiguousarray(bin_off, dtype=np.int64)
+        if blob.size == 0:
+            blob = np.zeros(1, np.uint8)
+        self._check(self.lib.sp_length_bins_set(self.h, off.size - 1, _ptr(blob), _ptr(off)))
+
+    def length_bins_sample(self, cumulative: np.ndarray, target_coverage_bp: int):
+        cum = np.ascontiguousarray(cumulative, dtype=np.float64)
+        n, b, a, e = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        hist = np.zeros(cum.size, np.int32)
+        self._check(self.lib.sp_length_bins_sample(self.h, _ptr(cum), cum.size, int(target_coverage_bp), C.byref(n), C.byref(b),
+                                                   C.byref(a), C.byref(e), _ptr(hist)))
+        return dict(n_reads=n.value, fastq_bytes=b.value, attempts=a.value, bases=e.value, histogram=hist)
+
+    def length_bins_copy(self, capacity: int, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty(max(capacity, 1), dtype=np.uint8)
+        w = C.c_int64()
+        self._check(self.lib.sp_length_bins_copy(self.h, _ptr(out), out.size, C.byref(w)))
+        return out[:w.value]
+
+    def length_bins_timing(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(self.lib.sp_length_bins_timing(self.h, C.byref(a), C.byref(b)))
+        return dict(sample_ms=a.value, copy_ms=b.value)

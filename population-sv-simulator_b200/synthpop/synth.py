@@ -246,3 +246,50 @@ def write_hmm_model(path: str, seed: int = GENERATOR_SEED, accuracies=range(74, 
             for s in range(1, n_states + 1):
                 tp = rng.dirichlet([1.5] * n_states)
                 f.write(f"{acc} TP {s} " + " ".join(f"{x:.6f}" for x in tp) + "\n")
+
+
+def cumulative_bimodal(n_bins: int, bin_length: int, mean_left: float, std_left: float, mean_right: float,
+                       std_right: float, weight_left: float) -> np.ndarray:
+    """buildCumulativeBimodal (src/SampleReadsFromLengthBins.java:87-102) with libm erf in place of commons-math3's
+    NormalDistribution.probability — the table is an INPUT of the native side (the Java host computes it with
+    commons-math; last-ulp differences between the two erf implementations are outside the drop-in boundary)."""
+    import math
+
+    def prob(mean, sd, x0, x1):
+        d = sd * math.sqrt(2.0)
+        return 0.5 * (math.erf((x1 - mean) / d) - math.erf((x0 - mean) / d))
+
+    c = np.array([prob(mean_left, std_left, i * bin_length, (i + 1) * bin_length) * weight_left +
+                  prob(mean_right, std_right, i * bin_length, (i + 1) * bin_length) * (1.0 - weight_left)
+                  for i in range(n_bins)], dtype=np.float64)
+    s = 0.0
+    for v in c:  # same summation order as the Java loop
+        s += float(v)
+    c = c / s
+    for i in range(1, n_bins):
+        c[i] = c[i] + c[i - 1]
+    return c
+
+
+def write_length_bins(prefix: str, n_bins: int, bin_length: int, records_per_bin, seed: int = GENERATOR_SEED,
+                      with_names: bool = True) -> int:
+    """Length-bin files in the format BuildReadLengthBins writes (src/BuildReadLengthBins.java:42-105): file
+    <prefix><i>.bin holds 4-line FASTQ records whose sequence length lies in [i*bin_length, (i+1)*bin_length).
+    records_per_bin: int or sequence of n_bins ints. Returns the total number of sequence bases written."""
+    rng = np.random.default_rng(seed + 11)
+    per = [int(records_per_bin)] * n_bins if np.isscalar(records_per_bin) else [int(x) for x in records_per_bin]
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    total = 0
+    for b in range(n_bins):
+        parts = []
+        for j in range(per[b]):
+            lo = max(1, b * bin_length)
+            ln = int(rng.integers(lo, (b + 1) * bin_length))
+            seq = acgt[rng.integers(0, 4, size=ln)].tobytes()
+            qual = (rng.integers(33 + 20, 33 + 60, size=ln).astype(np.uint8)).tobytes()
+            name = (f"@m64_{b}_{j}/ccs" if with_names else "@r").encode()
+            parts += [name, b"\n", seq, b"\n+\n", qual, b"\n"]
+            total += ln
+        with open(f"{prefix}{b}.bin", "wb") as f:
+            f.write(b"".join(parts))
+    return total
