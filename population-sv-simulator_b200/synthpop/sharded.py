@@ -1,0 +1,107 @@
+"""Sharding of one SimulateHaplotypes run across the GPUs of a box: one process per GPU,
+`torch.distributed` for the plumbing.
+
+Individuals (pairs of consecutive haplotype ids) are split in contiguous blocks, the way the reference's WDL scatters
+them (wdl/SimulateHaplotypes.wdl:142-163). The prologue (loadReference, model, loadPositions, sampleVariants) is a pure
+function of (inputs, seed), so every rank computes the same variant table and nothing is broadcast. The genotype cells
+are index-addressable (src/SimulateHaplotypes.java:621-634: cell (j,i) uses LCG steps S1+2(j*H+i)), so a rank draws only
+its own columns. The ONE exchange is after the collision fixer: per-variant carrier counts (int32[V]) are all-gathered
+and summed (AF_j := carriers_j / H, :986; isActive, :693-706) and the per-haplotype lists are all-gathered for the joint
+VCF's HAPLOTYPES= field and haplotype2variants.txt, which rank 0 writes. Materialisation and reads need no traffic.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def shard_of_individuals(n_individuals: int, rank: int, world: int) -> tuple[int, int]:
+    """Individuals [a, b) owned by `rank`: the first (n mod world) ranks get one more (100 over 8 -> 13,13,13,13,12,...)."""
+    base, extra = divmod(n_individuals, world)
+    a = rank * base + min(rank, extra)
+    return a, a + base + (1 if rank < extra else 0)
+
+
+def shard_of_haplotypes(n_individuals: int, rank: int, world: int) -> tuple[int, int]:
+    """Inclusive haplotype range [first, last] of `rank` (haplotypes 2k and 2k+1 belong to individual k); (0, -1) if empty."""
+    a, b = shard_of_individuals(n_individuals, rank, world)
+    return (2 * a, 2 * b - 1) if b > a else (0, -1)
+
+
+def allgather_counts(local_counts, dist, group=None):
+    """Sum over ranks of the per-variant carrier counts through ONE all-gather (a tensor on the backend's device:
+    CUDA for nccl, CPU for gloo). Returns the global counts as a tensor on the same device."""
+    import torch
+    world = dist.get_world_size(group)
+    gathered = torch.empty(world * local_counts.numel(), dtype=local_counts.dtype, device=local_counts.device)
+    dist.all_gather_into_tensor(gathered, local_counts.contiguous().view(-1), group=group)
+    return gathered.view(world, -1).sum(dim=0, dtype=torch.int32)
+
+
+def allgather_lists(local_off: np.ndarray, local_ids: np.ndarray, dist, device, group=None):
+    """All-gather of the ranks' CSR haplotype lists (rank order = haplotype order). Returns (all_off, all_ids) as numpy."""
+    import torch
+    world = dist.get_world_size(group)
+    n_h = int(local_off.size - 1)
+    meta = torch.tensor([n_h, int(local_ids.size)], dtype=torch.int64, device=device)
+    metas = torch.empty(world * 2, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(metas, meta, group=group)
+    metas = metas.view(world, 2).cpu().numpy()
+    max_h, max_ids = int(metas[:, 0].max()), int(metas[:, 1].max())
+    lens = torch.zeros(max(max_h, 1), dtype=torch.int64, device=device)
+    if n_h:
+        lens[:n_h] = torch.from_numpy(np.diff(local_off).astype(np.int64)).to(device)
+    ids = torch.zeros(max(max_ids, 1), dtype=torch.int32, device=device)
+    if local_ids.size:
+        ids[:local_ids.size] = torch.from_numpy(np.ascontiguousarray(local_ids, dtype=np.int32)).to(device)
+    all_lens = torch.empty(world * lens.numel(), dtype=torch.int64, device=device)
+    all_ids = torch.empty(world * ids.numel(), dtype=torch.int32, device=device)
+    dist.all_gather_into_tensor(all_lens, lens, group=group)
+    dist.all_gather_into_tensor(all_ids, ids, group=group)
+    all_lens, all_ids = all_lens.view(world, -1).cpu().numpy(), all_ids.view(world, -1).cpu().numpy()
+    lens_cat = np.concatenate([all_lens[r, : metas[r, 0]] for r in range(world)]) if world else np.zeros(0, np.int64)
+    ids_cat = np.concatenate([all_ids[r, : metas[r, 1]] for r in range(world)]) if world else np.zeros(0, np.int32)
+    off = np.concatenate(([0], np.cumsum(lens_cat))).astype(np.int64)
+    return off, ids_cat.astype(np.int32)
+
+
+class _DeviceInt32:
+    """__cuda_array_interface__ view of a device buffer the library owns (no copy)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def simulate_population_sharded(ctx, argv, dist=None, write_files: bool = True):
+    """SimulateHaplotypes.main (src/SimulateHaplotypes.java:75-116) across the ranks of `dist` (None = single process).
+    Every rank calls this with the same argv and a context created with the same seed. Returns a dict with the rank's
+    haplotype range and the global counts. Afterwards the context holds the rank's haplotype lists, ready for
+    sp_plan_haplotypes / the read kernel on the rank's own individuals."""
+    import torch
+    rank = dist.get_rank() if dist is not None else 0
+    world = dist.get_world_size() if dist is not None else 1
+    n_individuals = int(argv[9])
+    if n_individuals < world:
+        raise ValueError(f"{n_individuals} individuals cannot be sharded over {world} ranks")
+    first, last = shard_of_haplotypes(n_individuals, rank, world)
+    ctx.population_begin(argv, first, last)
+    info = ctx.population_info()
+    n_local = max(0, last - first + 1)
+    if dist is None or world == 1:
+        ctx.population_finish(None, None, None, 1 if write_files else 2)
+        return dict(first=first, last=last, counts=ctx.population_local_counts(), n_variants=info["n_variants"])
+    nccl = dist.get_backend() == "nccl"
+    device = torch.device("cuda", torch.cuda.current_device()) if nccl else torch.device("cpu")
+    V = info["n_variants"]
+    if nccl:
+        ctx.synchronize()
+        local = torch.as_tensor(_DeviceInt32(ctx.population_counts_device(), V), device=device)  # zero-copy: the library's buffer
+    else:
+        local = torch.from_numpy(ctx.population_local_counts().copy())
+    counts = allgather_counts(local, dist).cpu().numpy().astype(np.int32)
+    off, ids = ctx.population_local_lists(n_local)
+    all_off, all_ids = allgather_lists(off, ids, dist, device)
+    if write_files:
+        ctx.population_finish(counts, all_off if rank == 0 else None, all_ids if rank == 0 else None, 1 if rank == 0 else 0)
+    else:
+        ctx.population_finish(counts, None, None, 2)
+    return dict(first=first, last=last, counts=counts, n_variants=V, all_off=all_off, all_ids=all_ids)
