@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
 #include <string>
 #include <vector>
 #include "synthpop_cuda.h"
@@ -27,7 +28,7 @@ int main(int argc, char** argv) {
         else break;
     }
     if (a >= argc) {
-        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes> <positional argv of the Java class>\n");
+        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|pbsim> <argv of the reference's command>\n");
         return 2;
     }
     const std::string cls = argv[a++];
@@ -52,6 +53,70 @@ int main(int argc, char** argv) {
         pa.n_insertion_strings = atoi(args[6]); pa.allele_frequency_threshold = atof(args[7]);
         pa.n_variants_frequent = atoi(args[8]); pa.n_individuals = atoi(args[9]); pa.output_dir = args[10];
         rc = sp_simulate_population(ctx, &pa);
+    } else if (cls == "SampleReadsFromLengthBins") {
+        // MEAN_LEFT STD_LEFT MEAN_RIGHT STD_RIGHT WEIGHT_LEFT BIN_LENGTH MAX_READ_LENGTH BINS_PREFIX
+        // GENOME_LENGTH_EACH_HAPLOTYPE TARGET_COVERAGE_EACH_HAPLOTYPE OUTPUT_FASTQ_FILE (src/SampleReadsFromLengthBins.java:20-30)
+        if (args.size() < 11) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
+        const double ml = atof(args[0]), sl = atof(args[1]), mr = atof(args[2]), sr = atof(args[3]), wl = atof(args[4]);
+        sp_length_bin_args la;
+        la.bin_length = atoi(args[5]); la.max_read_length = atoi(args[6]); la.bins_prefix = args[7];
+        la.genome_length_each_haplotype = atoll(args[8]); la.target_coverage_each_haplotype = atof(args[9]);
+        la.output_fastq_file = args[10];
+        if (la.bin_length <= 0) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArithmeticException: / by zero\n"); return 1; }
+        // buildCumulativeBimodal (:87-102). The Java host uses commons-math3's NormalDistribution.probability; this C++
+        // host has only libm erf, which can differ from it in the last ulp (documented in INTEGRATION.md).
+        const int nb = (la.max_read_length + la.bin_length - 1) / la.bin_length;
+        std::vector<double> c(nb > 0 ? nb : 0);
+        auto prob = [](double m, double sd, double x0, double x1) {
+            const double d = sd * std::sqrt(2.0);
+            return 0.5 * (std::erf((x1 - m) / d) - std::erf((x0 - m) / d));
+        };
+        double sum = 0.0;
+        for (int i = 0; i < nb; i++) {
+            c[i] = prob(ml, sl, (double)i * la.bin_length, (double)(i + 1) * la.bin_length) * wl +
+                   prob(mr, sr, (double)i * la.bin_length, (double)(i + 1) * la.bin_length) * (1.0 - wl);
+            sum += c[i];
+        }
+        for (int i = 0; i < nb; i++) c[i] /= sum;
+        for (int i = 1; i < nb; i++) c[i] += c[i - 1];
+        la.cumulative = c.data();
+        rc = sp_sample_reads_from_bins(ctx, &la);
+    } else if (cls == "pbsim") {
+        // the long options of docker/pbsim2.cpp:195-213 that model mode uses, then the FASTA (docker/haplotype2reads.sh:53)
+        sp_read_args ra;
+        memset(&ra, 0, sizeof ra);
+        ra.depth = ra.length_mean = ra.length_sd = ra.accuracy_mean = ra.accuracy_min = ra.accuracy_max = -1.0;
+        ra.length_min = ra.length_max = -1; ra.sub_ratio = ra.ins_ratio = ra.del_ratio = -1;
+        ra.seed = (uint32_t)seed;
+        const char* fasta = nullptr;
+        for (size_t i = 0; i < args.size(); i++) {
+            const std::string o = args[i];
+            if (o.rfind("--", 0) != 0) { fasta = args[i]; continue; }
+            if (i + 1 >= args.size()) { fprintf(stderr, "ERROR: option %s needs a value\n", o.c_str()); return 255; }
+            const char* v = args[++i];
+            if (o == "--depth") ra.depth = atof(v);
+            else if (o == "--length-mean") ra.length_mean = atof(v);
+            else if (o == "--length-sd") ra.length_sd = atof(v);
+            else if (o == "--length-min") ra.length_min = atoll(v);
+            else if (o == "--length-max") ra.length_max = atoll(v);
+            else if (o == "--accuracy-mean") ra.accuracy_mean = atof(v);
+            else if (o == "--accuracy-min") ra.accuracy_min = atof(v);
+            else if (o == "--accuracy-max") ra.accuracy_max = atof(v);
+            else if (o == "--difference-ratio") { if (sscanf(v, "%d:%d:%d", &ra.sub_ratio, &ra.ins_ratio, &ra.del_ratio) != 3) { fprintf(stderr, "ERROR: (difference-ratio: %s) is not valid.\n", v); return 255; } }
+            else if (o == "--hmm_model") ra.hmm_model = v;
+            else if (o == "--prefix") ra.prefix = v;
+            else if (o == "--id-prefix") ra.id_prefix = v;
+            else if (o == "--seed") ra.seed = (uint32_t)strtoul(v, nullptr, 10);
+            else if (o == "--no-error") ra.no_error = atoi(v);  // docker/pbsim2noError.cpp
+            else { fprintf(stderr, "ERROR: option %s is not part of model mode\n", o.c_str()); return 255; }
+        }
+        if (!fasta) { fprintf(stderr, "ERROR: no reference FASTA\n"); return 255; }
+        rc = sp_simulate_reads(ctx, &ra, fasta);
+        if (rc != SP_OK) {  // pbsim: message on stderr + exit(-1) (docker/pbsim2.cpp:233-236)
+            fprintf(stderr, "%s\n", sp_last_error(ctx));
+            sp_destroy(ctx);
+            return 255;
+        }
     } else {
         fprintf(stderr, "synthpop: unknown class %s\n", cls.c_str());
         sp_destroy(ctx);

@@ -1,0 +1,63 @@
+import java.lang.foreign.*;
+import java.lang.invoke.MethodHandle;
+import static java.lang.foreign.ValueLayout.*;
+
+/**
+ * Panama FFM (JDK 22+) binding of libsynthpop_cuda.so: one downcall handle per entry point of include/synthpop_cuda.h
+ * that the three command-line classes need. Not compiled in the build image (no JDK there); compile where a JDK
+ * exists with `javac -cp commons-math3-3.6.1.jar *.java` and run with `--enable-native-access=ALL-UNNAMED
+ * -Djava.library.path=<dir of libsynthpop_cuda.so>`.
+ */
+final class SynthpopNative {
+    static final Linker LINKER = Linker.nativeLinker();
+    static final SymbolLookup LIB = SymbolLookup.libraryLookup(System.mapLibraryName("synthpop_cuda"), Arena.global());
+
+    private static MethodHandle h(String name, FunctionDescriptor d) {
+        return LINKER.downcallHandle(LIB.find(name).orElseThrow(() -> new UnsatisfiedLinkError(name)), d);
+    }
+
+    static final MethodHandle sp_create = h("sp_create", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_LONG));
+    static final MethodHandle sp_destroy = h("sp_destroy", FunctionDescriptor.ofVoid(ADDRESS));
+    static final MethodHandle sp_last_error = h("sp_last_error", FunctionDescriptor.of(ADDRESS, ADDRESS));
+    static final MethodHandle sp_simulate_population = h("sp_simulate_population", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle sp_print_haplotypes = h("sp_print_haplotypes",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    static final MethodHandle sp_sample_reads_from_bins = h("sp_sample_reads_from_bins", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+
+    /** sp_population_args (include/synthpop_cuda.h): argv of SimulateHaplotypes.main, src/SimulateHaplotypes.java:76-86. */
+    static final StructLayout POPULATION_ARGS = MemoryLayout.structLayout(
+            ADDRESS.withName("model_dir"), ADDRESS.withName("population_name"), ADDRESS.withName("reference_file"),
+            ADDRESS.withName("repeat_intervals_file"), ADDRESS.withName("segdups_file"), ADDRESS.withName("insertion_strings_file"),
+            JAVA_INT.withName("n_insertion_strings"), MemoryLayout.paddingLayout(4),
+            JAVA_DOUBLE.withName("allele_frequency_threshold"), JAVA_INT.withName("n_variants_frequent"),
+            JAVA_INT.withName("n_individuals"), ADDRESS.withName("output_dir"));
+
+    /** sp_length_bin_args: argv[5..10] of SampleReadsFromLengthBins.main + the cumulative table. */
+    static final StructLayout LENGTH_BIN_ARGS = MemoryLayout.structLayout(
+            ADDRESS.withName("cumulative"), JAVA_INT.withName("bin_length"), JAVA_INT.withName("max_read_length"),
+            ADDRESS.withName("bins_prefix"), JAVA_LONG.withName("genome_length_each_haplotype"),
+            JAVA_DOUBLE.withName("target_coverage_each_haplotype"), ADDRESS.withName("output_fastq_file"));
+
+    /** The one deviation from the reference argv: the RNG seed (the reference uses `new Random()`). */
+    static long seed() {
+        String s = System.getenv("SYNTHPOP_SEED");
+        return s == null ? System.nanoTime() : Long.parseLong(s);
+    }
+
+    static MemorySegment create(Arena arena) throws Throwable {
+        MemorySegment out = arena.allocate(ADDRESS);
+        String dev = System.getenv("SYNTHPOP_DEVICE");
+        int rc = (int) sp_create.invokeExact(out, dev == null ? 0 : Integer.parseInt(dev), seed());
+        if (rc != 0) throw new IllegalStateException("sp_create failed: no usable CUDA device (there is no CPU fallback)");
+        return out.get(ADDRESS, 0);
+    }
+
+    /** 0 = ok; 3 = System.exit(3) of SampleReadsFromLengthBins; anything else = the Java exception named in the message. */
+    static void check(MemorySegment ctx, int rc) throws Throwable {
+        if (rc == 0) return;
+        MemorySegment msg = ((MemorySegment) sp_last_error.invokeExact(ctx)).reinterpret(Long.MAX_VALUE);
+        String text = msg.getString(0);
+        if (rc == 3) { System.err.println(text); System.exit(3); }
+        throw new RuntimeException(text);
+    }
+}
