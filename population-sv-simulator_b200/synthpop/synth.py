@@ -226,10 +226,17 @@ def generate_population_inputs(root: str, length: int, seed: int = GENERATOR_SEE
 
 
 def write_hmm_model(path: str, seed: int = GENERATOR_SEED, accuracies=range(74, 101), n_states: int = 5,
-                    n_columns: int = 94) -> None:
+                    n_columns: int = 94, quality: str = "high") -> None:
     """Synthetic quality-code HMM in the text format set_hmm_model parses (docker/pbsim2.cpp:2583-2647):
     "<acc> IP <state> <p>", "<acc> EP <state> <94 emission probabilities>", "<acc> TP <state> <p_1..p_n>".
-    (The real P6C4.model is not part of the reference repository.)"""
+    (The real P6C4.model is not part of the reference repository.)
+
+    quality="phred": the emission windows of accuracy class a are centred on the Phred value of its error rate,
+    -10*log10((100.5-a)/100) (Q6 at 74 %, Q13 at 95 %, Q23 at 100 %), shifted by 2 per state — what a model trained on
+    real reads looks like, since PBSIM2 groups training reads by the accuracy their qualities imply.
+    quality="high": centres at (a-70)*0.9+3*state (Q16..Q42): a stress case for the deletion rejection loop, whose
+    acceptance probability is 10^(-q/10) (docker/pbsim2.cpp:2284-2292)."""
+    import math
     rng = np.random.default_rng(seed + 3)
     with open(path, "w") as f:
         for acc in accuracies:
@@ -237,7 +244,11 @@ def write_hmm_model(path: str, seed: int = GENERATOR_SEED, accuracies=range(74, 
             for s in range(1, n_states + 1):
                 f.write(f"{acc} IP {s} {ip[s - 1]:.6f}\n")
             for s in range(1, n_states + 1):
-                centre = min(n_columns - 2, max(2, int(round((acc - 70) * 0.9 + 3 * s))))
+                if quality == "phred":
+                    centre = int(round(-10.0 * math.log10((100.5 - acc) / 100.0))) + 2 * (s - (n_states + 1) // 2)
+                else:
+                    centre = int(round((acc - 70) * 0.9 + 3 * s))
+                centre = min(n_columns - 2, max(2, centre))
                 w = np.zeros(n_columns)
                 lo, hi = max(0, centre - 6), min(n_columns, centre + 7)
                 w[lo:hi] = rng.random(hi - lo) + 0.05
