@@ -73,11 +73,11 @@ CCS_CLI = ["--length-min", "5000", "--length-max", "30000", "--accuracy-min", "0
 READ_ALGO_BYTES_PER_BASE = 2.0  # 1 B of haplotype read + 1 B of read written per emitted base
 
 
-def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch):
+def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, quality="phred"):
     """BASELINE configs[3] on this GPU's shard: pbsim2-model CCS reads at `depth`x over `n_haps` chr1-sized haplotypes that
     were materialised on the device and never leave it. Returns the `reads` object of the bench line."""
     model = os.path.join(work, "P6C4_synthetic.model")
-    synth.write_hmm_model(model)
+    synth.write_hmm_model(model, quality=quality)
     args, _ = splib.ReadArgs.from_options(CCS_CLI + ["--depth", str(depth), "--hmm_model", model, "--seed", "42"],
                                           stream_mode=splib.READS_PER_READ_STREAMS)
     ctx.reads_configure(args)
@@ -99,10 +99,13 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch):
         k_ms += tm["kernel_ms"]; p_ms += tm["plan_ms"]
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of the last haplotype's reads
+    draws_per_base = float(used.astype(np.int64).sum()) / max(1, r["bases"])
     achieved = READ_ALGO_BYTES_PER_BASE * bases / (k_ms / 1e3) / 1e9
     return {"metric": "CCS read Gbp/s", "value": bases / dt / 1e9, "unit": "Gbp/s",
             "workload": f"pbsim2 model mode, {depth}x over {n_haps} materialised chr1-sized haplotypes, length 15000+-2000 in [5000,30000], "
-                        "accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model, per-read glibc streams",
+                        f"accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model ({quality} emission centres), per-read glibc streams",
+            "draws_per_base": round(draws_per_base, 2),
             "reads": reads, "dropped_NNNNN": dropped, "bases": bases, "wall_s": dt, "kernel_ms": k_ms, "host_plan_ms": p_ms,
             "kernel_gbp_s": bases / (k_ms / 1e3) / 1e9, "gpu_launches": ctx.kernel_launches - l0,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -120,7 +123,7 @@ def reads_cpu_baseline(synth, work, L=1_500_000, depth=30):
     synth.write_fasta(fa, ">chr1_0", bases)
     model = os.path.join(work, "P6C4_synthetic.model")
     if not os.path.exists(model):
-        synth.write_hmm_model(model)
+        synth.write_hmm_model(model, quality="phred")
     t0 = time.perf_counter()
     subprocess.run([exe] + CCS_CLI + ["--depth", str(depth), "--hmm_model", model, "--seed", "42", "--prefix",
                                       os.path.join(work, "cpu_reads"), fa], check=True, stderr=subprocess.DEVNULL)
@@ -193,6 +196,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--read-haplotypes", type=int, default=2, help="haplotypes of the CCS read leg (0 = skip)")
     ap.add_argument("--read-depth", type=int, default=30)
+    ap.add_argument("--read-quality", default="phred", choices=["phred", "high"], help="emission centres of the synthetic HMM quality model")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -323,7 +327,7 @@ def main():
     if args.read_haplotypes > 0:
         peak, peak_kind = measured_peak_gbs()
         a0 = (rank * args.read_haplotypes) % (N_HAPLOTYPES - args.read_haplotypes)
-        reads_obj = reads_leg(ctx, splib, synth, work, a0, args.read_haplotypes, args.read_depth, peak, torch)
+        reads_obj = reads_leg(ctx, splib, synth, work, a0, args.read_haplotypes, args.read_depth, peak, torch, args.read_quality)
         if dist is not None:
             tr = torch.tensor([reads_obj["wall_s"], reads_obj["kernel_ms"]], dtype=torch.float64, device="cuda")
             dist.all_reduce(tr, op=dist.ReduceOp.MAX)
