@@ -25,14 +25,7 @@ GlibcRand::GlibcRand(unsigned seed) {
     for (int i = 0; i < 310; i++) next();
     count = 0;
 }
-GlibcRand GlibcRand::interleaved(unsigned seed, long ref_num, long read_index) {
-    GlibcRand g(1);
-    for (int l = 0; l < 32; l++) g.lanes.emplace_back(read_seed(seed, ref_num, read_index, l));
-    g.count = 0;
-    return g;
-}
 int GlibcRand::next() {
-    if (!lanes.empty()) return lanes[count++ % 32].next();
     r[f] += r[b];
     const int result = (int)(r[f] >> 1);
     if (++f >= 31) f = 0;
@@ -323,7 +316,7 @@ void simulate_by_model(const Params& p, const Tables& t, const std::string& ref_
     Mut m;
     char idbuf[256];
     while (len_total < len_quota) {
-        if (p.per_read_streams) rng = GlibcRand::interleaved(p.seed, ref_num, res_num);
+        if (p.per_read_streams) rng = GlibcRand(read_seed(p.seed, ref_num, res_num));
         const uint64_t draws_at_start = rng.count;
         if (log) log->draw_offset.push_back(rng.count);
         long index = rng.next() % t.len_rand_value + 1;

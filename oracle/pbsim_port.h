@@ -26,19 +26,17 @@ struct Params {  // the options docker/haplotype2reads.sh:32 passes, with pbsim'
     std::string id_prefix = "S";
     bool no_error = false;  // pbsim2noError.cpp: print mut.seq instead of mut.new_seq
     // Production mode of the GPU read kernel (NOT a reference behaviour; the reference has one global rand() stream
-    // whose per-read start is data-dependent): every read draws from its own 32 glibc streams, stream l seeded with
-    // srand(read_seed(seed, ref_num, read_index, l)), and the read's k-th rand() call returns the next value of stream
-    // k mod 32 (so that a warp generates 32 consecutive draws with one independent recurrence per lane). Everything
-    // else is the reference's algorithm, so this mode pins the kernel's per-read-stream output the same way the
-    // default mode pins its replay output.
+    // whose per-read start is data-dependent): every read draws from its own glibc stream, srand(read_seed(seed,
+    // ref_num, read_index)). Everything else is the reference's algorithm, so this mode pins the kernel's
+    // per-read-stream output the same way the default mode pins its replay output.
     bool per_read_streams = false;
 };
 
-// Seed of stream `lane` of read `read_index` (0-based) of sequence `ref_num` (1-based) in per-read-stream mode:
-// splitmix64 finaliser of the values, mapped to [1, 2^31-2].
-inline unsigned read_seed(unsigned seed, long ref_num, long read_index, int lane) {
+// Seed of read `read_index` (0-based) of sequence `ref_num` (1-based) in per-read-stream mode: splitmix64 finaliser
+// of the three values, mapped to [1, 2^31-2].
+inline unsigned read_seed(unsigned seed, long ref_num, long read_index) {
     uint64_t z = (uint64_t)seed * 0x9E3779B97F4A7C15ULL + (uint64_t)ref_num * 0xBF58476D1CE4E5B9ULL +
-                 ((uint64_t)read_index * 32 + (uint64_t)lane) * 0x94D049BB133111EBULL;
+                 (uint64_t)read_index * 0x94D049BB133111EBULL;
     z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ULL;
     z ^= z >> 27; z *= 0x94D049BB133111EBULL;
     z ^= z >> 31;
@@ -75,9 +73,7 @@ struct GlibcRand {  // srand(seed); rand()
     uint32_t r[34];
     int f, b;
     uint64_t count = 0;  // draws taken so far
-    std::vector<GlibcRand> lanes;  // per-read-stream mode: 32 interleaved streams (empty otherwise)
     explicit GlibcRand(unsigned seed);
-    static GlibcRand interleaved(unsigned seed, long ref_num, long read_index);
     int next();
 };
 

@@ -1,22 +1,20 @@
 // Row P of SURVEY.md §8a — the read kernel: the reference's patched PBSIM2 in model mode
 // (simulate_by_model docker/pbsim2.cpp:1641-1711, mutate :2260-2413), re-designed for B200.
 //
-// One WARP per read, persistent CTAs pulling read indices from a counter. Every random decision of the reference is a
-// glibc rand() call; a read consumes its draws in a fixed phase order (Appendix A.6), so the warp keeps a sliding window
-// of the read's draw stream on chip (shared-memory ring, bank-conflict-free for stride 1, 2, 16 and 32) and every phase
-// indexes it:
-//   stream .... per-read glibc stream generated by the warp itself: the TYPE_3 additive-feedback generator
-//               r[i] = r[i-31] + r[i-3] advances 31 outputs per step with a stride-3 shuffle scan (production mode), or
-//               coalesced loads of the reference's logged draws (replay mode).
-//   quality ... HMM chain state_i = tran2state[state_{i-1}][draw]: sequential in the reference. Each lane owns 16
-//               consecutive positions of a 512-position tile, carries the map {start state -> state} as 4-bit nibbles
-//               until all start states have merged, the 32 maps are composed with a shuffle scan, and only the
-//               pre-merge positions are replayed with the true incoming state. Uniform-quality accuracies are a lookup.
-//   deletions . rejection sampling, 32 attempts per step decided by ballot; the accepted positions become per-position
-//               byte counters (their prefix sums are the template shifts later).
-//   bases ..... 32 output bases per step: template gather (strand, uppercase), one draw each; the first lane with a
-//               substitution/insertion event (ballot + ffs) consumes its extra draws and the step is cut there, because
-//               later lanes' draw indices shift. Output bytes go through a shared-memory stage to 16-byte stores.
+// Every random decision of the reference is one glibc rand() call and a read consumes its draws in a data-dependent
+// order (Appendix A.6): quality chain, deletion rejection loop, start offset, then one draw per base plus 1-2 per
+// error event. The work per base is a few dozen dependent integer operations and no reuse, so the design is
+// ONE THREAD PER READ (first version: one warp per read around a shared-memory draw ring — 16 warp instructions per
+// base, most of them cooperation overhead; see profiles/r01_reads_kernel.md):
+//   * the thread runs the reference's loops as they are, with the glibc TYPE_3 generator r[i] = r[i-31] + r[i-3] as
+//     a 31-word circular buffer in shared memory laid out [word][thread] (bank = thread: conflict-free whatever
+//     each thread's phase), one add per draw;
+//   * a warp takes 32 reads that the host has grouped by (accuracy class, length), so its threads run the same
+//     phases for nearly the same trip counts;
+//   * per-read scratch (quality codes and deletion counters, one byte per position) lives in HBM interleaved
+//     [word][lane], so the sequential passes are 128-byte coalesced and only the rejection loop's lookups scatter;
+//   * the haplotype window is read in aligned 8-byte chunks and the read is written in aligned 8-byte chunks.
+// Replay mode feeds the same code from the reference's logged draws instead of the generator.
 // Everything is integer arithmetic; the only floating-point expressions of the reference's loop (:1682, :2282) are
 // evaluated on the host with the reference's own types when the per-read plan is made.
 #include "reads.h"
@@ -25,27 +23,17 @@
 
 namespace sp {
 
-constexpr int RD_RING = 2048;                       // draws of the current read kept on chip, per warp
-constexpr int RD_RING_WORDS = RD_RING + RD_RING / 32;  // one padding word per 32
-constexpr int RD_WARPS = 4;
-constexpr int RD_STAGE = 1024 + 64;                 // output staging bytes per warp
-constexpr int RD_TILE = 512;                        // quality positions per tile (16 per lane)
+constexpr int RD_THREADS = 128;  // reads in flight per CTA
 constexpr unsigned FULL = 0xffffffffu;
 
-// Seed of stream `lane` of read `read_index` (0-based) of sequence `ref_num` in per-read-stream mode: splitmix64
-// finaliser -> [1, 2^31-2].
-__host__ __device__ inline uint32_t read_seed(uint32_t seed, int64_t ref_num, int64_t read_index, int lane) {
+// Seed of read `read_index` (0-based) of sequence `ref_num` in per-read-stream mode: splitmix64 finaliser -> [1, 2^31-2].
+__host__ __device__ inline uint32_t read_seed(uint32_t seed, int64_t ref_num, int64_t read_index) {
     uint64_t z = (uint64_t)seed * 0x9E3779B97F4A7C15ULL + (uint64_t)ref_num * 0xBF58476D1CE4E5B9ULL +
-                 ((uint64_t)read_index * 32 + (uint64_t)lane) * 0x94D049BB133111EBULL;
+                 (uint64_t)read_index * 0x94D049BB133111EBULL;
     z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ULL;
     z ^= z >> 27; z *= 0x94D049BB133111EBULL;
     z ^= z >> 31;
     return (uint32_t)(1 + z % 2147483646ULL);
-}
-
-__device__ __forceinline__ int ring_addr(uint32_t idx) {
-    const uint32_t m = idx & (RD_RING - 1);
-    return (int)(m + (m >> 5));
 }
 
 __device__ __forceinline__ uint32_t fastmod(uint32_t a, uint32_t M, uint32_t sh, uint32_t d) {
@@ -66,7 +54,7 @@ __device__ __forceinline__ FastMod make_fastmod_dev(uint32_t d) {
 }
 
 // glibc srand(s), 1 <= s <= 2^31-2 (random_r.c TYPE_3: degree 31, separation 3): r[i] = 16807 * r[i-1] mod (2^31-1), then
-// 310 outputs of r[f] += r[b] (f = 3, b = 0 at the start) are discarded. Afterwards r[(3+j) % 31] is the j-th oldest word.
+// 310 outputs of r[f] += r[b] (f = 3, b = 0 at the start) are discarded; afterwards f is 3 again.
 __device__ __forceinline__ void glibc_seed(uint32_t s, uint32_t (&r)[31]) {
     uint64_t w = s;
     r[0] = s;
@@ -79,50 +67,36 @@ __device__ __forceinline__ void glibc_seed(uint32_t s, uint32_t (&r)[31]) {
     }
 }
 
-// The read's draw stream. Production mode: 32 independent glibc streams, one per lane; the read's k-th rand() call is the
-// next value of stream k mod 32, so row R of the ring (draws 32R..32R+31) is one step of every lane's own recurrence
-// z[R] = z[R-31] + z[R-3] — the ring itself is the generator state (raw words are stored, rand() = word >> 1).
-// Replay mode: coalesced loads of the reference's logged draws.
-struct WarpStream {
-    uint32_t gen;  // draws produced so far = stream index of the next one (a multiple of 32)
-    const int32_t* replay;
-    uint32_t* ring;
-    int lane;
-
-    __device__ __forceinline__ int row(uint32_t R) const { return (int)((R & (RD_RING / 32 - 1)) * 33 + lane); }
+// The read's rand(): the thread's own glibc generator (state column in shared memory) or the replayed log.
+template <bool REPLAY>
+struct DrawStream {
+    uint32_t* st;           // &state[0][thread]; word j of this thread is st[j * RD_THREADS]
+    const int32_t* replay;  // first logged draw of this read
+    uint32_t used;          // rand() calls so far
+    int f;                  // glibc's front index (rear = f - 3 mod 31)
     __device__ __forceinline__ void seed(uint32_t s) {
         uint32_t r[31];
         glibc_seed(s, r);
-        __syncwarp();
 #pragma unroll
-        for (int j = 0; j < 31; j++) ring[row((uint32_t)(RD_RING / 32 - 31 + j))] = r[(3 + j) % 31];  // rows -31..-1
-        gen = 0;
-        __syncwarp();
+        for (int j = 0; j < 31; j++) st[j * RD_THREADS] = r[j];
+        f = 3; used = 0;
     }
-    // make draws [.., upto) available; indices below upto - (RD_RING - 1024) may no longer be valid afterwards
-    __device__ __forceinline__ void ensure(uint32_t upto) {
-        if (gen >= upto) return;
-        __syncwarp();
-        if (replay) {
-            while (gen < upto) { ring[row(gen >> 5)] = (uint32_t)__ldg(replay + gen + lane) << 1; gen += 32; }
-        } else {
-            while (gen < upto) {  // three rows per step: they depend on rows R-31..R-29 and R-3..R-1 only
-                const uint32_t R = gen >> 5;
-                const uint32_t a0 = ring[row(R - 31)], a1 = ring[row(R - 30)], a2 = ring[row(R - 29)];
-                const uint32_t b0 = ring[row(R - 3)], b1 = ring[row(R - 2)], b2 = ring[row(R - 1)];
-                ring[row(R)] = a0 + b0; ring[row(R + 1)] = a1 + b1; ring[row(R + 2)] = a2 + b2;
-                gen += 96;
-            }
-        }
-        __syncwarp();
+    __device__ __forceinline__ uint32_t next() {
+        if (REPLAY) return (uint32_t)__ldg(replay + used++);
+        const int b = f >= 3 ? f - 3 : f + 28;
+        const uint32_t v = st[f * RD_THREADS] + st[b * RD_THREADS];
+        st[f * RD_THREADS] = v;
+        f = f == 30 ? 0 : f + 1;
+        used++;
+        return v >> 1;
     }
-    __device__ __forceinline__ uint32_t at(uint32_t idx) const { return ring[ring_addr(idx)] >> 1; }
 };
 
 struct ReadJob {
     const uint8_t* seq;  // the sequence reads are drawn from (a haplotype resident in HBM)
     int64_t L;
     int64_t n_reads;
+    const int32_t* order; // read indices grouped by (accuracy class, length): 32 consecutive entries share a warp
     const int32_t* len;   // emitted length per read (:1642-1650, quota clipping applied)
     const uint8_t* acc;   // accuracy class (:1654-1655)
     const int32_t* ndel;  // del_num_total (:2282)
@@ -135,413 +109,262 @@ struct ReadJob {
     uint8_t* out;
     uint8_t* dropped;
     uint32_t* used;
-    uint8_t* scratch;           // per warp: quality codes [0, stride/2), deletion counters [stride/2, stride)
-    int64_t scratch_stride;
+    uint32_t* scratch;          // per warp: [2][scratch_words][32] words — quality codes, then deletion counters
+    int64_t scratch_words;      // words per lane per array (4 positions each)
     unsigned long long* ctr;    // [0] next read, [1] error code, [2] error read, [3] dropped reads, [4] dropped bytes
     char id[64];                // ">" + id_prefix + ref_num + "_"
     int32_t id_len;
 };
 
-__device__ __forceinline__ uint32_t hmm_tran(const ReadTablesDev& T, int a51, uint32_t st, uint32_t d) {
-    return __ldg(T.tran2state + (a51 + st) * 101 + fastmod(d, T.mod_tran + a51 + st) + 1);
-}
-
-__device__ __forceinline__ uint64_t compose_maps(uint64_t G, uint64_t F, int ns) {  // s -> F[G[s]]
-    uint64_t r = 0;
-    for (int s = 1; s <= ns; s++) {
-        const uint32_t g = (uint32_t)(G >> (4 * s)) & 15u;
-        r |= ((F >> (4 * g)) & 15ull) << (4 * s);
-    }
-    return r;
-}
-
-// One tile of the HMM quality chain (:1657-1671): positions [i0, i0+512), lane owns 16 consecutive ones.
-// Position 0 has no transition (its state is the initial state). Returns the state after the tile.
-__device__ uint32_t hmm_tile(const ReadTablesDev& T, const WarpStream& S, int acc, int ns, uint32_t st_in, int i0, int len,
-                             uint8_t* q, int lane) {
-    const int a51 = acc * 51;
-    const int pbase = i0 + 16 * lane;
-    const uint64_t mask = ((ns >= 15) ? ~0ull : ((1ull << (4 * (ns + 1))) - 1)) & ~0xFull;  // nibbles 1..ns
-    uint64_t fmap = 0xFEDCBA9876543210ull & mask, chain = 0;
-    int m = 16;
-    bool merged = (ns == 1);
-    uint32_t st = 1;
-    if (merged) m = 0;
-#pragma unroll 1
-    for (int k = 0; k < 16; k++) {
-        const int p = pbase + k;
-        const bool live = p > 0 && p < len;
-        const uint32_t d = live ? S.at(2 + 2 * p) : 0;
-        if (merged) {
-            if (live) st = hmm_tran(T, a51, st, d);
-            chain |= (uint64_t)st << (4 * k);
-        } else {
-            if (live) {
-                uint64_t nf = 0;
-                for (int s = 1; s <= ns; s++)
-                    nf |= (uint64_t)hmm_tran(T, a51, (uint32_t)(fmap >> (4 * s)) & 15u, d) << (4 * s);
-                fmap = nf;
-            }
-            const uint64_t first = (fmap >> 4) & 15ull;
-            if (fmap == ((first * 0x1111111111111110ull) & mask)) {
-                merged = true; st = (uint32_t)first; m = k;
-                chain |= first << (4 * k);
-            }
-        }
-    }
-    if (merged) fmap = ((uint64_t)st * 0x1111111111111110ull) & mask;
-    uint64_t F = fmap;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint64_t G = __shfl_up_sync(FULL, F, d);
-        if (lane >= d) F = compose_maps(G, F, ns);
-    }
-    const uint64_t Fin = __shfl_up_sync(FULL, F, 1);
-    const uint64_t Flast = __shfl_sync(FULL, F, 31);
-    uint32_t s_in = lane == 0 ? st_in : (uint32_t)(Fin >> (4 * st_in)) & 15u;
-    // replay the pre-merge positions with the true incoming state
-    st = s_in;
-#pragma unroll 1
-    for (int k = 0; k < m; k++) {
-        const int p = pbase + k;
-        if (p > 0 && p < len) st = hmm_tran(T, a51, st, S.at(2 + 2 * p));
-        chain |= (uint64_t)st << (4 * k);
-    }
-    // emissions
-    uint32_t wq[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int p = pbase + k;
-        if (p < len) {
-            const uint32_t s = (uint32_t)(chain >> (4 * k)) & 15u;
-            const uint32_t e = __ldg(T.emis2qc + (a51 + s) * 101 + fastmod(S.at(3 + 2 * p), T.mod_emis + a51 + s) + 1);
-            wq[k >> 2] |= e << (8 * (k & 3));
-        }
-    }
-    if (pbase < len) *(uint4*)(q + pbase) = make_uint4(wq[0], wq[1], wq[2], wq[3]);
-    return (uint32_t)(Flast >> (4 * st_in)) & 15u;
-}
-
-// Models with state indices above 15 do not fit the nibble maps: lane 0 walks the tile like the reference does.
-__device__ uint32_t hmm_tile_serial(const ReadTablesDev& T, const WarpStream& S, int acc, uint32_t st_in, int i0, int len,
-                                    uint8_t* q, int lane) {
-    uint32_t st = st_in;
-    if (lane == 0) {
-        const int a51 = acc * 51;
-        const int end = min(len, i0 + RD_TILE);
-        for (int p = i0; p < end; p++) {
-            if (p > 0) st = hmm_tran(T, a51, st, S.at(2 + 2 * p));
-            q[p] = __ldg(T.emis2qc + (a51 + st) * 101 + fastmod(S.at(3 + 2 * p), T.mod_emis + a51 + st) + 1);
-        }
-    }
-    return __shfl_sync(FULL, st, 0);
-}
-
-__device__ __forceinline__ uint8_t fetch_base(const uint8_t* win, int32_t lenp, int32_t t, bool fwd) {  // :2316-2341
-    uint8_t c = __ldg(win + (fwd ? t : lenp - 1 - t));
-    if (c >= 'a' && c <= 'z') c -= 32;
-    if (!fwd) c = c == 'A' ? 'T' : c == 'T' ? 'A' : c == 'G' ? 'C' : c == 'C' ? 'G' : c;
-    return c;
-}
-
-struct OutStage {
-    uint8_t* stage;
-    uint8_t* out;
-    int64_t gbase;  // global offset of stage[0], a multiple of 16
-    int fill, lo;   // stage[lo, fill) holds bytes not yet written
-    int lane;
-    __device__ __forceinline__ void begin(uint8_t* st, uint8_t* o, int64_t at, int ln) {
-        stage = st; out = o; lane = ln;
-        gbase = at & ~15ll; lo = (int)(at & 15); fill = lo;
-    }
-    __device__ __forceinline__ void flush(bool final) {
-        __syncwarp();
-        const int nvec = fill >> 4;
-        for (int v = lane; v < nvec; v += 32) {
-            if (v == 0 && lo > 0) { for (int b = lo; b < 16; b++) out[gbase + b] = stage[b]; }
-            else *(uint4*)(out + gbase + 16 * v) = *(const uint4*)(stage + 16 * v);
-        }
-        if (final) {
-            for (int b = 16 * nvec + lane; b < fill; b += 32)
-                if (b >= lo) out[gbase + b] = stage[b];
-        } else {
-            const int rem = fill - 16 * nvec;
-            __syncwarp();
-            const uint8_t t = lane < rem ? stage[16 * nvec + lane] : 0;
-            __syncwarp();
-            if (lane < rem) stage[lane] = t;
-            gbase += 16 * nvec;
-            fill = rem;
-            if (nvec > 0) lo = 0;
-        }
-        __syncwarp();
-    }
-    // lanes [0, cnt) contribute one byte each
-    __device__ __forceinline__ void put(uint8_t c, int cnt) {
-        if (lane < cnt) stage[fill + lane] = c;
-        fill += cnt;
-        if (fill >= 512) flush(false);
-    }
-};
-
-// "NNNNN" detector over the emitted bytes (:1711): nrun = trailing N's so far (capped at 4)
-__device__ __forceinline__ void n_run_update(unsigned bits, int cnt, int& nrun, bool& drop) {
-    const unsigned long long c = ((unsigned long long)bits << nrun) | ((1ull << nrun) - 1);
-    if (c & (c >> 1) & (c >> 2) & (c >> 3) & (c >> 4)) drop = true;
-    const int total = cnt + nrun;
-    const unsigned long long inv = ~c & ((1ull << total) - 1);
-    const int trailing = inv == 0 ? total : total - 1 - (63 - __clzll((long long)inv));
-    nrun = min(4, trailing);
-}
-
 __device__ __forceinline__ void job_error(const ReadJob& J, int code, int64_t r) {
     if (atomicCAS(&J.ctr[1], 0ull, (unsigned long long)code) == 0ull) J.ctr[2] = (unsigned long long)r;
 }
 
-__global__ void __launch_bounds__(RD_WARPS * 32)
-reads_kernel(const ReadJob J, const ReadTablesDev T) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int32_t s_thre[3 * PB_NQ];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t* ring = (uint32_t*)smem + w * RD_RING_WORDS;
-    uint8_t* stage = smem + (size_t)RD_WARPS * RD_RING_WORDS * 4 + (size_t)w * RD_STAGE;
-    for (int i = threadIdx.x; i < 3 * PB_NQ; i += blockDim.x) s_thre[i] = T.thre[i];
-    __syncthreads();
-    const int64_t gw = (int64_t)blockIdx.x * RD_WARPS + w;
-    uint8_t* q = J.scratch + gw * J.scratch_stride;
-    uint32_t* delcnt = (uint32_t*)(q + J.scratch_stride / 2);
-    const uint8_t* delcnt8 = (const uint8_t*)delcnt;
+// The oriented, upper-cased template (:2316-2341): seq[t] for t in [0, len'), fetched through aligned 8-byte chunks.
+// The strand is data (a step of +-1 and an xor mask), not a branch: the threads of a warp alternate strands.
+struct Template {
+    const uint8_t* origin;  // address of seq[0]: first base of the window (+) or its last base (-)
+    int32_t dir;            // +1 / -1
+    uint32_t rev;           // 0 / 0xff
+    int64_t cur;            // index of the cached chunk on the 8-byte grid of the address space
+    uint64_t chunk;
+    __device__ __forceinline__ void begin(const uint8_t* w, int32_t lp, bool forward) {
+        origin = forward ? w : w + (lp - 1); dir = forward ? 1 : -1; rev = forward ? 0u : 0xffu; cur = -1; chunk = 0;
+    }
+    __device__ __forceinline__ uint8_t at(int32_t t) {
+        const uintptr_t a = (uintptr_t)(origin + (int64_t)dir * t);
+        const int64_t id = (int64_t)(a >> 3);
+        if (id != cur) { chunk = __ldg((const unsigned long long*)(a & ~(uintptr_t)7)); cur = id; }
+        uint32_t c = (uint32_t)(chunk >> (8 * (a & 7))) & 0xffu;
+        c -= (c - 'a' <= 'z' - 'a') ? 32u : 0u;  // toupper
+        // complement: A(0x41)<->T(0x54) differ by 0x15, C(0x43)<->G(0x47) by 0x04; anything else stays
+        const uint32_t x = (c == 'A' || c == 'T') ? 0x15u : (c == 'C' || c == 'G') ? 0x04u : 0u;
+        return (uint8_t)(c ^ (x & rev));
+    }
+};
 
-    for (;;) {
-        unsigned long long rr = 0;
-        if (lane == 0) rr = atomicAdd(&J.ctr[0], 1ull);
-        const int64_t r = (int64_t)__shfl_sync(FULL, rr, 0);
-        if (r >= J.n_reads) break;
-        const int32_t len = J.len[r], ndel = J.ndel[r];
-        const int acc = J.acc[r];
-        const int32_t lenp = len + ndel;
-        const int64_t rec0 = J.rec_off[r];
-        if (len < 2 || lenp >= J.L) {  // rand() % (len-1) with len 1 traps in the reference; len' >= ref.len changes the output length
-            if (lane == 0) { job_error(J, len < 2 ? 1 : 2, r); J.dropped[r] = 1; J.used[r] = 0; }
-            continue;
+// The read's bases go out in aligned 8-byte words at a pace that depends on the base index only (every 8th base), so
+// the threads of a warp stay in step whatever the alignment of their records: word m of the record's 8-byte grid is
+// assembled from the previous and the current group of 8 bases by a funnel shift.
+struct SeqOut {
+    uint8_t* out;
+    int64_t seq0;    // global offset of base 0
+    uint32_t a8;     // 8 * (seq0 & 7)
+    uint64_t prev, cur;
+    __device__ __forceinline__ void begin(uint8_t* o, int64_t at) { out = o; seq0 = at; a8 = 8u * (uint32_t)(at & 7); prev = 0; cur = 0; }
+    __device__ __forceinline__ void put(int32_t k, uint8_t c) {
+        cur |= (uint64_t)c << (8 * (k & 7));
+        if ((k & 7) == 7) {
+            const int64_t g = (seq0 & ~7ll) + (k - 7);  // aligned address of the word that can be completed now
+            if (k == 7) {                                // the first word shares its low bytes with the header
+                for (uint32_t b = a8; b < 64; b += 8) out[g + (b >> 3)] = (uint8_t)(cur >> (b - a8));
+            } else {
+                const uint64_t w = a8 ? (prev >> (64 - a8)) | (cur << a8) : cur;
+                *(uint64_t*)(out + g) = w;
+            }
+            prev = cur; cur = 0;
         }
-        WarpStream S;
-        S.lane = lane; S.ring = ring; S.gen = 0;
-        if (J.replay) S.replay = J.replay + J.replay_off[r];
-        else { S.replay = nullptr; S.seed(read_seed(J.seed, J.ref_num, r, lane)); }
+    }
+    // bases [0, n) were put; writes what is still pending, then the record's closing '\n'
+    __device__ __forceinline__ void finish(int32_t n) {
+        const int32_t done = n >= 8 ? (n & ~7) - (int32_t)(a8 >> 3) : 0;  // stream bytes already in memory
+        for (int32_t i = done; i < n; i++) {
+            const uint64_t src = (i >> 3) == (n >> 3) ? cur : prev;
+            out[seq0 + i] = (uint8_t)(src >> (8 * (i & 7)));
+        }
+        out[seq0 + n] = '\n';
+    }
+};
 
-        // ---- quality codes (:1657-1680)
-        uint32_t D0;
-        if (T.exist_hmm[acc]) {
-            const int ns = T.nstates[acc];
-            S.ensure(4);
-            uint32_t st = __ldg(T.init2state + acc * 101 + fastmod(S.at(2), T.mod_init + acc) + 1);
-#pragma unroll 1
-            for (int i0 = 0; i0 < len; i0 += RD_TILE) {
-                S.ensure(2 + 2 * (uint32_t)min(len, i0 + RD_TILE));
-                st = ns <= 15 ? hmm_tile(T, S, acc, ns, st, i0, len, q, lane) : hmm_tile_serial(T, S, acc, st, i0, len, q, lane);
-            }
-            D0 = 2 + 2 * (uint32_t)len;
-        } else {
-            const uint4 mf = __ldg((const uint4*)(T.mod_freq + acc));
-            const uint8_t* f2q = T.freq2qc + acc * 1001;
-#pragma unroll 1
-            for (int i0 = 0; i0 < len; i0 += RD_TILE) {
-                S.ensure(2 + (uint32_t)min(len, i0 + RD_TILE));
-                const int pbase = i0 + 16 * lane;
-                uint32_t wq[4] = {0, 0, 0, 0};
-#pragma unroll
-                for (int k = 0; k < 16; k++) {
-                    const int p = pbase + k;
-                    if (p < len) wq[k >> 2] |= (uint32_t)__ldg(f2q + fastmod(S.at(2 + p), mf.x, mf.y, mf.z) + 1) << (8 * (k & 3));
-                }
-                if (pbase < len) *(uint4*)(q + pbase) = make_uint4(wq[0], wq[1], wq[2], wq[3]);
-            }
-            D0 = 2 + (uint32_t)len;
-        }
-        __syncwarp();
+__device__ __forceinline__ uint32_t hmm_tran(const ReadTablesDev& T, int a51, uint32_t st, uint32_t d) {
+    return __ldg(T.tran2state + (a51 + st) * 101 + fastmod(d, T.mod_tran + a51 + st) + 1);
+}
+__device__ __forceinline__ uint32_t hmm_emis(const ReadTablesDev& T, int a51, uint32_t st, uint32_t d) {
+    return __ldg(T.emis2qc + (a51 + st) * 101 + fastmod(d, T.mod_emis + a51 + st) + 1);
+}
 
-        // ---- deletions by rejection (:2282-2292): attempt a uses draws D0+2a (position) and D0+2a+1 (value)
-        uint32_t O = D0;
-        if (ndel > 0) {
-            for (int i = lane; i < (len + 3) / 4; i += 32) delcnt[i] = 0;
-            __syncwarp();
-            const FastMod ml = make_fastmod_dev((uint32_t)(len - 1));
-            uint32_t a = 0;
-            int got = 0;
-            for (;;) {  // 4 x 32 attempts per step: the four quality lookups (L2 latency) are in flight together
-                S.ensure(D0 + 2 * (a + 128));
-                uint32_t pos[4], v[4];
-                unsigned bal[4];
-                bool ok[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const uint32_t idx = D0 + 2 * (a + 32 * u + lane);
-                    pos[u] = fastmod(S.at(idx), ml.M, ml.sh, ml.d);
-                    v[u] = S.at(idx + 1) % 1000000u;
-                }
-                int qv[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) qv[u] = q[pos[u]];
-                int total = 0;
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    ok[u] = (int32_t)v[u] < s_thre[qv[u]];
-                    bal[u] = __ballot_sync(FULL, ok[u]);
-                    total += __popc(bal[u]);
-                }
-                const bool done = got + total >= ndel;
-                int need = ndel - got;  // acceptances still wanted (only meaningful when done)
-                uint32_t consumed = 128;
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    int last = 31;
-                    bool active = true;
-                    if (done) {
-                        const int c = __popc(bal[u]);
-                        if (need <= 0) active = false;                                   // attempts the reference never made
-                        else if (need <= c) { last = (int)__fns(bal[u], 0, need); consumed = 32 * u + last + 1; }
-                        need -= c;
-                    }
-                    if (active && ok[u] && lane <= last) {
-                        const uint32_t sh = 8 * (pos[u] & 3);
-                        const uint32_t old = atomicAdd(&delcnt[pos[u] >> 2], 1u << sh);
-                        if (((old >> sh) & 255u) == 255u) job_error(J, 3, r);
-                    }
-                }
-                a += consumed;
-                if (done) break;
-                got += total;
-            }
-            __syncwarp();
-            O = D0 + 2 * a;
-        }
+// One read, start to end, by one thread (simulate_by_model :1657-1711 + mutate :2260-2413).
+template <bool REPLAY>
+__device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTablesDev& T, const int32_t* s_thre, DrawStream<REPLAY>& S,
+                                              uint32_t* qw, uint32_t* dw, int64_t r, unsigned mask) {
+    // `mask` = the lanes of this warp that hold a read. Trip counts differ a little between the threads of a warp; the
+    // __syncwarp(mask) after every phase makes them start the next one together (independent thread scheduling would
+    // otherwise let them drift apart for the rest of the read, one thread per issue slot).
+    int32_t len = J.len[r], ndel = J.ndel[r];
+    const int acc = J.acc[r];
+    const int32_t lenp = len + ndel;
+    const int64_t rec0 = J.rec_off[r];
+    const bool bad = len < 2 || lenp >= J.L;  // rand() % (len-1) with len 1 traps in the reference; len' >= ref.len changes the output length
+    if (bad) {
+        job_error(J, len < 2 ? 1 : 2, r);
+        len = 0; ndel = 0;  // every loop below runs zero times; the thread still joins the warp's phase barriers
+    }
+    if (REPLAY) { S.replay = J.replay + J.replay_off[r]; S.used = 0; }
+    else S.seed(read_seed(J.seed, J.ref_num, r));
+    S.next(); S.next();  // the length and accuracy draws (:1642, :1654), evaluated on the host when the plan was made
+    __syncwarp(mask);
 
-        // ---- start offset (:2306-2311), header, bases (:2348-2401)
-        S.ensure(O + 1);
-        const uint32_t offset = S.at(O) % (uint32_t)(J.L - lenp + 1);
-        const uint32_t E0 = O + 1;
-        const bool fwd = (r & 1) == 0;  // res_num % 2 == 0 before the increment (:2316)
-        const uint8_t* win = J.seq + offset;
-        OutStage OS;
-        OS.begin(stage, J.out, rec0, lane);
-        if (lane == 0) {  // ">S<ref>_<n>Z"
-            int f = OS.fill;
-            for (int i = 0; i < J.id_len; i++) stage[f++] = (uint8_t)J.id[i];
-            char dig[24];
-            int nd = 0;
-            for (long long v = r + 1; v > 0; v /= 10) dig[nd++] = (char)('0' + v % 10);
-            while (nd > 0) stage[f++] = (uint8_t)dig[--nd];
-            stage[f++] = 'Z';
-            OS.fill = f;
+    // ---- quality codes (:1657-1680), four per scratch word; the deletion counters are cleared on the way
+    if (T.exist_hmm[acc]) {
+        const int a51 = acc * 51;
+        uint32_t st = __ldg(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);
+        uint32_t word = 0;
+#pragma unroll 1
+        for (int32_t p = 0; p < len; p++) {
+            if (p > 0) st = hmm_tran(T, a51, st, S.next());
+            word |= hmm_emis(T, a51, st, S.next()) << (8 * (p & 3));
+            if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
         }
-        OS.fill = __shfl_sync(FULL, OS.fill, 0);
-        __syncwarp();
+        if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; }
+    } else {
+        const uint4 mf = __ldg((const uint4*)(T.mod_freq + acc));
+        const uint8_t* f2q = T.freq2qc + acc * 1001;
+        uint32_t word = 0;
+#pragma unroll 1
+        for (int32_t p = 0; p < len; p++) {
+            word |= (uint32_t)__ldg(f2q + fastmod(S.next(), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
+            if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+        }
+        if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; }
+    }
+    __syncwarp(mask);
 
-        uint32_t X = 0, I = 0, dels_run = 0;
-        int nrun = 0;
-        bool drop = false;
-        const bool emit = !J.no_error;
+    // ---- deletions by rejection (:2282-2292). The loop is driven by a warp vote so that the threads stay in step.
+    {
+        const FastMod ml = make_fastmod_dev((uint32_t)max(len - 1, 1));
+        int32_t num = 0;
 #pragma unroll 1
-        for (int i0 = 0; i0 < len; i0 += 32) {
-            // 32 output bases per step. A substitution/insertion at lane f consumes 1-2 extra draws and (insertion) holds
-            // the template back, which shifts the draw index and the template index of every later lane: the lanes after
-            // f re-evaluate with the corrected offsets, one cheap round per event, instead of cutting the step at f.
-            const int n = min(32, len - i0);
-            const bool valid = lane < n;
-            S.ensure(E0 + i0 + X + n + 66);
-            const int i = i0 + lane;
-            uint32_t incl = 0, dc = 0;
-            if (ndel > 0) {
-                dc = valid ? __ldcg(delcnt8 + i) : 0;  // the counters were built by L2 atomics
-                incl = dc;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const uint32_t o = __shfl_up_sync(FULL, incl, d);
-                    if (lane >= d) incl += o;
+        for (;;) {
+            const bool more = num < ndel;
+            if (!__any_sync(mask, more)) break;
+            if (more) {
+                const uint32_t pos = fastmod(S.next(), ml.M, ml.sh, ml.d);
+                const int32_t v = (int32_t)(S.next() % 1000000u);
+                const uint32_t sh = 8 * (pos & 3);
+                const int qv = (qw[(pos >> 2) * 32] >> sh) & 255u;
+                if (v < s_thre[qv]) {
+                    const uint32_t d = dw[(pos >> 2) * 32];
+                    if (((d >> sh) & 255u) == 255u) job_error(J, 3, r);
+                    dw[(pos >> 2) * 32] = d + (1u << sh);
+                    num++;
                 }
-            }
-            const int32_t tb = (int32_t)(i + dels_run + incl - dc);  // template index before insertions are counted
-            const int qv = valid ? q[i] : 0;
-            const int32_t t_sub = s_thre[PB_NQ + qv], t_ins = s_thre[2 * PB_NQ + qv];
-            uint32_t Xl = X, Il = I, own_extra = 0, own_ins = 0;
-            uint8_t outc = 0;
-            bool settled = !valid;  // lanes whose draw has been examined with final offsets and found event-free, or events
-            bool is_event = false;
-#pragma unroll 1
-            for (;;) {
-                const int32_t d = settled ? 0x7fffffff : (int32_t)(S.at(E0 + i + Xl) % 1000000u);
-                const bool sub = d < t_sub;
-                const bool ins = !sub && d < t_ins;
-                const unsigned ev = __ballot_sync(FULL, sub || ins);
-                if (ev == 0) break;
-                const int f = __ffs(ev) - 1;
-                if (lane == f) {
-                    const uint8_t nt = fetch_base(win, lenp, tb - (int32_t)Il, fwd);
-                    const uint32_t base = E0 + i + Xl;
-                    if (sub) {  // :2362-2378, per-base tables of set_mut :2211-2214
-                        uint32_t idx = S.at(base + 1) % 3u;
-                        own_extra = 1;
-                        if (nt == 'A') outc = "TGC"[idx];
-                        else if (nt == 'T') outc = "AGC"[idx];
-                        else if (nt == 'G') outc = "ATC"[idx];
-                        else if (nt == 'C') outc = "ATG"[idx];
-                        else { idx = S.at(base + 2) % 4u; outc = "ATGC"[idx]; own_extra = 2; }
-                    } else {    // :2379-2387: the template base is not consumed
-                        const uint32_t idx = S.at(base + 1) % 8u;
-                        outc = idx >= 4 ? nt : (uint8_t)"ATGC"[idx];
-                        own_extra = 1; own_ins = 1;
-                    }
-                    is_event = true;
-                }
-                const uint32_t e = __shfl_sync(FULL, own_extra, f), isf = __shfl_sync(FULL, own_ins, f);
-                if (lane <= f) settled = true;  // lanes before f saw their final draw and had no event
-                else { Xl += e; Il += isf; }
-                if (f + 1 >= n) break;
-            }
-            if (valid && !is_event) outc = fetch_base(win, lenp, tb - (int32_t)Il, fwd);
-            X = __shfl_sync(FULL, Xl + own_extra, n - 1);
-            I = __shfl_sync(FULL, Il + own_ins, n - 1);
-            if (ndel > 0) dels_run += __shfl_sync(FULL, incl, n - 1);
-            if (emit) {
-                const unsigned nb = __ballot_sync(FULL, valid && outc == 'N');
-                if (nb == 0) nrun = 0;
-                else n_run_update(nb, n, nrun, drop);
-                OS.put(outc, n);
-            }
-        }
-        if (!emit) {  // pbsim2noError.cpp:1711 prints mut.seq, the oriented template of length len'
-#pragma unroll 1
-            for (int i0 = 0; i0 < lenp; i0 += 32) {
-                const int n = min(32, lenp - i0);
-                const uint8_t c = lane < n ? fetch_base(win, lenp, i0 + lane, fwd) : 0;
-                const unsigned nb = __ballot_sync(FULL, lane < n && c == 'N');
-                n_run_update(nb, n, nrun, drop);
-                OS.put(c, n);
-            }
-        }
-        OS.put('\n', 1);
-        OS.flush(true);
-        if (lane == 0) {
-            J.dropped[r] = drop ? 1 : 0;
-            J.used[r] = E0 + (uint32_t)len + X;
-            if (drop) {
-                atomicAdd(&J.ctr[3], 1ull);
-                atomicAdd(&J.ctr[4], (unsigned long long)(J.rec_off[r + 1] - rec0));
             }
         }
     }
+
+    // ---- start offset (:2306-2311), header, bases (:2348-2401)
+    const uint32_t offset = bad ? 0u : S.next() % (uint32_t)(J.L - lenp + 1);
+    const bool fwd = (r & 1) == 0;  // res_num % 2 == 0 before the increment (:2316)
+    Template Tm;
+    Tm.begin(J.seq + offset, lenp, fwd);
+    int64_t o = rec0;
+    if (!bad) {  // ">S<ref>_<n>Z", a dozen bytes
+        for (int i = 0; i < J.id_len; i++) J.out[o++] = (uint8_t)J.id[i];
+        char dig[20];
+        int nd = 0;
+        for (long long v = r + 1; v > 0; v /= 10) dig[nd++] = (char)('0' + v % 10);
+        while (nd > 0) J.out[o++] = (uint8_t)dig[--nd];
+        J.out[o++] = 'Z';
+    }
+    SeqOut O;
+    O.begin(J.out, o);
+    const bool emit = !J.no_error;
+    int nrun = 0;
+    bool drop = false;
+    int32_t t = 0;  // template index: advances with every base except after an insertion, and over deleted bases
+    uint32_t wq = 0, wd = 0;
+    __syncwarp(mask);
+#pragma unroll 1
+    for (int32_t k = 0;; k++) {
+        const bool more = k < len;
+        if (!__any_sync(mask, more)) break;
+        if (more) {
+            if ((k & 3) == 0) { wq = qw[(k >> 2) * 32]; wd = ndel > 0 ? dw[(k >> 2) * 32] : 0u; }
+            const int qv = wq & 255u; wq >>= 8;
+            const int32_t dc = wd & 255u; wd >>= 8;
+            const uint8_t nt = Tm.at(t);
+            const int32_t d = (int32_t)(S.next() % 1000000u);
+            uint8_t outc = nt;
+            int32_t adv = 1;
+            if (d < s_thre[2 * PB_NQ + qv]) {  // an error event: ins_thre >= sub_thre (:1455-1459), so one test screens both
+                if (d < s_thre[PB_NQ + qv]) {  // substitution (:2362-2378), per-base tables of set_mut :2211-2214
+                    uint32_t idx = S.next() % 3u;
+                    if (nt == 'A') outc = "TGC"[idx];
+                    else if (nt == 'T') outc = "AGC"[idx];
+                    else if (nt == 'G') outc = "ATC"[idx];
+                    else if (nt == 'C') outc = "ATG"[idx];
+                    else { idx = S.next() % 4u; outc = "ATGC"[idx]; }
+                } else {                       // insertion (:2379-2387): the template base is not consumed
+                    const uint32_t idx = S.next() % 8u;
+                    if (idx < 4) outc = "ATGC"[idx];
+                    adv = 0;
+                }
+            }
+            t += adv + dc;
+            if (emit) {
+                nrun = outc == 'N' ? nrun + 1 : 0;
+                drop |= nrun >= 5;
+                O.put(k, outc);
+            }
+        }
+    }
+    __syncwarp(mask);
+    if (bad) { J.dropped[r] = 1; J.used[r] = 0; return; }
+    if (emit) O.finish(len);
+    else {  // pbsim2noError.cpp:1711 prints mut.seq, the oriented template of length len'
+#pragma unroll 1
+        for (int32_t i = 0; i < lenp; i++) {
+            const uint8_t c = Tm.at(i);
+            nrun = c == 'N' ? nrun + 1 : 0;
+            drop |= nrun >= 5;
+            O.put(i, c);
+        }
+        O.finish(lenp);
+    }
+    J.dropped[r] = drop ? 1 : 0;
+    J.used[r] = S.used;
+    if (drop) {
+        atomicAdd(&J.ctr[3], 1ull);
+        atomicAdd(&J.ctr[4], (unsigned long long)(J.rec_off[r + 1] - rec0));
+    }
 }
 
-// First two draws of reads [r0, r0+n) in per-read-stream mode (length and accuracy, :1642, :1654): the first output of the
-// read's streams 0 and 1.
+template <bool REPLAY>
+__global__ void __launch_bounds__(RD_THREADS)
+reads_kernel(const ReadJob J, const ReadTablesDev T) {
+    __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
+    __shared__ int32_t s_thre[3 * PB_NQ];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 3 * PB_NQ; i += blockDim.x) s_thre[i] = T.thre[i];
+    __syncthreads();
+    const int64_t gw = (int64_t)blockIdx.x * (RD_THREADS / 32) + w;
+    uint32_t* qw = J.scratch + gw * 2 * J.scratch_words * 32 + lane;
+    uint32_t* dw = qw + J.scratch_words * 32;
+    DrawStream<REPLAY> S;
+    S.st = s_state + (REPLAY ? 0 : threadIdx.x);
+    S.replay = nullptr; S.used = 0; S.f = 3;
+    for (;;) {
+        unsigned long long b0 = 0;
+        if (lane == 0) b0 = atomicAdd(&J.ctr[0], 32ull);
+        const int64_t base = (int64_t)__shfl_sync(FULL, b0, 0);
+        if (base >= J.n_reads) break;
+        const int64_t my = base + lane;
+        const unsigned mask = __ballot_sync(FULL, my < J.n_reads);
+        if (my < J.n_reads) simulate_read<REPLAY>(J, T, s_thre, S, qw, dw, (int64_t)J.order[my], mask);
+        __syncwarp();
+    }
+}
+
+// First two draws of reads [r0, r0+n) in per-read-stream mode (length and accuracy, :1642, :1654).
 __global__ void __launch_bounds__(128)
 first_draws_kernel(uint32_t seed, int64_t ref_num, int64_t r0, int64_t n, int32_t* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 2 * n) return;
+    if (i >= n) return;
     uint32_t r[31];
-    glibc_seed(read_seed(seed, ref_num, r0 + (i >> 1), (int)(i & 1)), r);
-    out[i] = (int32_t)((r[3] + r[0]) >> 1);
+    glibc_seed(read_seed(seed, ref_num, r0 + i), r);
+    r[3] += r[0];
+    out[2 * i] = (int32_t)(r[3] >> 1);
+    out[2 * i + 1] = (int32_t)((r[4] + r[1]) >> 1);
 }
 
 // Kept records -> contiguous file bytes (only launched when some read was dropped).
@@ -602,7 +425,7 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
         int64_t n = (int64_t)((double)(quota - len_total) / mean_len * 1.05) + 1024;
         n = std::min<int64_t>(n, 1 << 26);
         R.d_first.reserve((size_t)n * 2);
-        first_draws_kernel<<<(unsigned)((2 * n + 127) / 128), 128, 0, st>>>(p.seed, ref_num, r0, n, R.d_first.p);
+        first_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(p.seed, ref_num, r0, n, R.d_first.p);
         c->launches++;
         SP_CUDA(cudaGetLastError());
         first.resize((size_t)n * 2);
@@ -659,29 +482,38 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     R.n_dropped = 0;
     if (n_reads == 0) return;
 
-    static bool attr_set = false;
-    const size_t smem = (size_t)RD_WARPS * (RD_RING_WORDS * 4 + RD_STAGE);
-    if (!attr_set) {
-        SP_CUDA(cudaFuncSetAttribute(reads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
+    // group the reads so that the 32 threads of a warp run nearly the same trip counts: longest first (tail balance),
+    // then by accuracy class (same tables, similar deletion loops). Counting sort, O(n).
+    {
+        const int32_t width = std::max(1, (max_len + 63) / 64);
+        std::vector<int32_t> count(64 * 101 + 1, 0);
+        auto key = [&](int64_t i) { return (63 - std::min(63, R.h_len[i] / width)) * 101 + (int)R.h_acc[i]; };
+        for (int64_t i = 0; i < n_reads; i++) count[key(i) + 1]++;
+        for (size_t k = 1; k < count.size(); k++) count[k] += count[k - 1];
+        R.h_order.resize((size_t)n_reads);
+        for (int64_t i = 0; i < n_reads; i++) R.h_order[(size_t)count[key(i)]++] = (int32_t)i;
+        R.d_order.reserve(n1);
+        SP_CUDA(cudaMemcpyAsync(R.d_order.p, R.h_order.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
     }
     int ctas_per_sm = 1;
-    SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel, RD_WARPS * 32, smem));
+    if (replay) SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<true>, RD_THREADS, 0));
+    else SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<false>, RD_THREADS, 0));
     ctas_per_sm = std::max(1, ctas_per_sm);
-    const int64_t want_ctas = (n_reads + RD_WARPS - 1) / RD_WARPS;
-    const int grid = (int)std::min<int64_t>(want_ctas, (int64_t)c->sm_count * ctas_per_sm);
-    const int64_t half = ((int64_t)max_len + 511) / 512 * 512 + 512;
-    const int64_t stride = 2 * half;
-    R.d_scratch.reserve((size_t)stride * grid * RD_WARPS, 0.0);
+    const int64_t want_ctas = (n_reads + RD_THREADS - 1) / RD_THREADS;
+    const int64_t grid_full = std::min<int64_t>(want_ctas, (int64_t)c->sm_count * ctas_per_sm);
+    const int64_t words = ((int64_t)max_len + 3) / 4 + 1;
+    const size_t cta_scratch = (size_t)(RD_THREADS / 32) * 2 * words * 32 * sizeof(uint32_t);
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(grid_full, (int64_t)((16ull << 30) / cta_scratch)));  // <= 16 GiB of scratch
+    R.d_scratch.reserve(cta_scratch * grid, 0.0);
 
     ReadJob J{};
-    J.seq = d_seq; J.L = L; J.n_reads = n_reads;
+    J.seq = d_seq; J.L = L; J.n_reads = n_reads; J.order = R.d_order.p;
     J.len = R.d_len.p; J.acc = R.d_acc.p; J.ndel = R.d_ndel.p; J.rec_off = R.d_rec_off.p;
     J.seed = p.seed; J.ref_num = ref_num; J.no_error = p.no_error ? 1 : 0;
     J.replay = replay ? R.d_replay.p : nullptr;
     J.replay_off = replay ? R.d_replay_off.p : nullptr;
     J.out = R.d_out.p; J.dropped = R.d_dropped.p; J.used = R.d_used.p;
-    J.scratch = R.d_scratch.p; J.scratch_stride = stride;
+    J.scratch = (uint32_t*)R.d_scratch.p; J.scratch_words = words;
     J.ctr = (unsigned long long*)R.d_ctr.p;
     if (id.size() >= sizeof J.id) throw Error(SP_ERR_ARG, "read id prefix too long");
     memcpy(J.id, id.data(), id.size());
@@ -689,7 +521,8 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     R.plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_plan0).count();
     if (!R.ev0) { SP_CUDA(cudaEventCreate(&R.ev0)); SP_CUDA(cudaEventCreate(&R.ev1)); }
     SP_CUDA(cudaEventRecord(R.ev0, st));
-    reads_kernel<<<grid, RD_WARPS * 32, smem, st>>>(J, R.dev);
+    if (replay) reads_kernel<true><<<grid, RD_THREADS, 0, st>>>(J, R.dev);
+    else reads_kernel<false><<<grid, RD_THREADS, 0, st>>>(J, R.dev);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     SP_CUDA(cudaEventRecord(R.ev1, st));
@@ -800,7 +633,7 @@ int sp_reads_set_replay(sp_ctx* ctx, const int32_t* draws, int64_t n_draws, cons
     if (!draws || !read_offsets || n_draws < 2 || n_reads < 1) throw Error(SP_ERR_ARG, "bad replay log");
     R.replay_draws.assign(draws, draws + n_draws);
     R.replay_off.assign(read_offsets, read_offsets + n_reads);
-    const size_t pad = sp::RD_RING + 64;  // the ring prefetches past a read's last draw
+    const size_t pad = 64;
     R.d_replay.reserve((size_t)n_draws + pad);
     R.d_replay_off.reserve((size_t)n_reads);
     SP_CUDA(cudaMemsetAsync(R.d_replay.p + n_draws, 0, pad * 4, ctx->stream));

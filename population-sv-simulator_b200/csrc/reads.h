@@ -78,8 +78,9 @@ struct ReadState {
     std::vector<uint8_t> h_acc, h_dropped;
     std::vector<int64_t> h_rec_off;
     std::vector<uint32_t> h_used;
+    std::vector<int32_t> h_order;
     bool results_on_host = false;
-    DevBuf<int32_t> d_len, d_ndel, d_replay, d_first;
+    DevBuf<int32_t> d_len, d_ndel, d_replay, d_first, d_order;
     DevBuf<uint8_t> d_acc, d_dropped, d_out, d_scratch, d_seq, d_compact;
     DevBuf<int64_t> d_rec_off, d_replay_off, d_koff;
     DevBuf<uint32_t> d_used;
