@@ -35,6 +35,12 @@ const char* sp_last_error(const sp_ctx* ctx);
 const char* sp_version(void);
 /* Launch on the caller's CUDA stream (cudaStream_t as void*); NULL = the context's own stream. */
 int sp_set_stream(sp_ctx* ctx, void* cuda_stream);
+/* Second stream for sp_population_genotypes (rows G/C/N): the genotype kernels and the serial collision fixer
+ * (src/SimulateHaplotypes.java:617-690) of the next batch then run under sp_materialise of the current one, which stays
+ * on the stream of sp_set_stream. Give this stream a HIGHER priority (cudaStreamCreateWithPriority): the hardware
+ * dispatches every tile of the copy kernel before a later grid of equal priority. The call still returns with the
+ * batch's lists complete. NULL = same stream. */
+int sp_set_population_stream(sp_ctx* ctx, void* cuda_stream);
 /* Number of kernels this library launched on ctx since creation (bench.py's gpu_launches). */
 int64_t sp_kernel_launches(const sp_ctx* ctx);
 

@@ -226,6 +226,7 @@ void sp_destroy(sp_ctx* ctx) {
     sp::free_population(ctx);
     sp::free_reads(ctx);
     sp::free_length_bins(ctx);
+    if (ctx->ev_plan) cudaEventDestroy(ctx->ev_plan);
     delete ctx;
     if (s) cudaStreamDestroy(s);
 }
@@ -235,6 +236,13 @@ const char* sp_last_error(const sp_ctx* ctx) { return ctx ? ctx->err.c_str() : "
 int sp_set_stream(sp_ctx* ctx, void* cuda_stream) {
     SP_API_BEGIN
     ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    SP_API_END
+}
+
+int sp_set_population_stream(sp_ctx* ctx, void* cuda_stream) {
+    SP_API_BEGIN
+    ctx->pop_stream = (cudaStream_t)cuda_stream;
+    if (cuda_stream && !ctx->ev_plan) SP_CUDA(cudaEventCreateWithFlags(&ctx->ev_plan, cudaEventDisableTiming));
     SP_API_END
 }
 

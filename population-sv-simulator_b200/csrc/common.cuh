@@ -72,6 +72,10 @@ struct sp_ctx {
     int64_t seed = 0;
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
+    // optional second stream for rows G/C/N (sp_set_population_stream): the genotype kernels and the serial collision
+    // fixer of batch s+1 then run under the materialisation kernel of batch s
+    cudaStream_t pop_stream = nullptr;
+    cudaEvent_t ev_plan = nullptr;   // recorded after plan_kernel has consumed the lists of the current batch
     std::string err;
     int64_t launches = 0;
     int sm_count = 148;

@@ -455,7 +455,9 @@ compact_count_kernel(const int64_t* __restrict__ off, const int32_t* __restrict_
 
 // ------------------------------------------------------------------------------------------------ host
 void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
-    cudaStream_t st = c->stream;
+    cudaStream_t st = c->pop_stream ? c->pop_stream : c->stream;
+    // the lists of the previous batch are free once its plan_kernel has read them
+    if (c->pop_stream && c->ev_plan) SP_CUDA(cudaStreamWaitEvent(st, c->ev_plan, 0));
     const int32_t V = P.n_variants, H = P.n_haplotypes_total, h0 = P.h0, Hl = P.h1 - P.h0;
     const int32_t W = (V + 31) / 32;
     P.d_thr.reserve(std::max(V, 1));

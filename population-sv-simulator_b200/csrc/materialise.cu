@@ -335,6 +335,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
                                     c->d_seg_base.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_hap_len.p, c->d_err.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());
+    if (c->ev_plan) SP_CUDA(cudaEventRecord(c->ev_plan, st));
     c->h_hap_len.assign(nh, 0);
     int32_t err[4] = {0, 0, 0, 0};
     SP_CUDA(cudaMemcpyAsync(c->h_hap_len.data(), c->d_hap_len.p, nh * 8, cudaMemcpyDeviceToHost, st));

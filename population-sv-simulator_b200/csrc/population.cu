@@ -161,7 +161,7 @@ void population_genotypes(sp_ctx* c, int32_t first, int32_t last) {
     run_genotype_and_collisions(c, P);
     c->v_off_dev = P.d_off2.p; c->v_ids_dev = P.d_ids2.p; c->v_off_host = P.h_off.data();
     c->v_h0 = first; c->v_n = last - first + 1;
-    c->plan_last = -1; c->plan_first = 0;
+    // the plan, segment tables and output slots of the previous batch stay valid until the next sp_plan_haplotypes
 }
 
 }  // namespace sp

@@ -112,6 +112,7 @@ def load() -> C.CDLL:
         "sp_last_error": (cp, [vp]),
         "sp_version": (cp, []),
         "sp_set_stream": (C.c_int, [vp, vp]),
+        "sp_set_population_stream": (C.c_int, [vp, vp]),
         "sp_kernel_launches": (i64, [vp]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
@@ -214,6 +215,9 @@ class Context:
     # -- plumbing
     def set_stream(self, cuda_stream: int | None):
         self._check(self.lib.sp_set_stream(self.h, C.c_void_p(cuda_stream or 0)))
+
+    def set_population_stream(self, cuda_stream: int | None):
+        self._check(self.lib.sp_set_population_stream(self.h, C.c_void_p(cuda_stream or 0)))
 
     def synchronize(self):
         self._check(self.lib.sp_synchronize(self.h))

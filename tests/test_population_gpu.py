@@ -118,3 +118,40 @@ def test_global_memory_collision_fixer_fallback(sp, oracle_bin, tmp_path, monkey
     ctx.simulate_haplotypes(inp.simulate_argv(got, 8, n_frequent=600))
     _cmp_dirs(want, got, 8)
     ctx.close()
+
+
+def test_pipelined_batches_on_population_stream(sp, oracle_bin, tmp_path):
+    """sp_set_population_stream: rows G/C/N of batch s+1 run on a second stream while batch s is being materialised;
+    every haplotype of every batch still equals the oracle's PrintHaplotypes output."""
+    import torch
+    from synthpop import synth
+    inp = synth.generate_population_inputs(str(tmp_path / "in"), 3_000_000, n_insertions=2000, seed=11)
+    want = str(tmp_path / "want"); hw = str(tmp_path / "hw")
+    os.makedirs(want); os.makedirs(hw)
+    n_ind = 12
+    argv = inp.simulate_argv(want, n_ind, n_frequent=500)
+    subprocess.run([oracle_bin, "--quiet", "--seed", "42", "SimulateHaplotypes"] + argv, check=True)
+    subprocess.run([oracle_bin, "--quiet", "PrintHaplotypes", "0", str(2 * n_ind - 1), inp.reference_file,
+                    want + "/haplotype2variants.txt", want + "/variants.txt", hw], check=True)
+    ctx = sp.Context(0, 42)
+    main, side = torch.cuda.Stream(), torch.cuda.Stream(priority=-1)
+    ctx.set_stream(main.cuda_stream)
+    ctx.population_begin(inp.simulate_argv(str(tmp_path / "got"), n_ind, n_frequent=500), 0, -1)
+    ctx.population_finish(None, None, None, 2)
+    ctx.set_population_stream(side.cuda_stream)
+    batch = 6
+    pending = None
+    for a in range(0, 2 * n_ind, batch):
+        ctx.population_genotypes(a, a + batch - 1)     # overlaps the previous batch's materialisation kernel
+        if pending is not None:                        # the previous batch is read back only now
+            pa, pstride = pending
+            for h in range(pa, pa + batch):
+                assert ctx.copy_haplotype(h, pstride).tobytes() == open(f"{hw}/haplotype_{h}.fa", "rb").read(), h
+        lens, stride = ctx.plan_haplotypes(a, a + batch - 1, True)
+        ctx.materialise()
+        pending = (a, stride)
+    pa, pstride = pending
+    for h in range(pa, pa + batch):
+        assert ctx.copy_haplotype(h, pstride).tobytes() == open(f"{hw}/haplotype_{h}.fa", "rb").read(), h
+    ctx.set_population_stream(None)
+    ctx.close()
