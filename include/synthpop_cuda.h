@@ -199,6 +199,35 @@ int sp_reads_device(sp_ctx* ctx, void** records, void** record_offsets, void** d
  * calling script at :54 and is not written.) */
 int sp_simulate_reads(sp_ctx* ctx, const sp_read_args* args, const char* fasta_path);
 
+/* ---- the tail of docker/haplotype2reads.sh and the coverage chunks of reads2svs.sh ------- */
+/* `cat reads_ID2.fa >> reads_ID1.fa; shuf; tr 'Z' '\n'` (docker/haplotype2reads.sh:59-63) on the device.
+ * begin: start a new individual. add: take the records of the last sp_reads_simulate_* call (ownership of the device
+ * buffers moves, nothing is copied); call it once per haplotype, ID1 first. finish: permute the lines and write the
+ * two-line FASTA records (">S1_<n>\n<seq>\n") into one device buffer. `shuf` is unseeded in the reference; here line k
+ * of the concatenated file gets the key "state of java.util.Random(shuffle_seed) after k+1 steps" and the lines are
+ * written in ascending key order. */
+int sp_reads_mix_begin(sp_ctx* ctx);
+int sp_reads_mix_add(sp_ctx* ctx);
+int sp_reads_mix_finish(sp_ctx* ctx, int64_t shuffle_seed, int64_t* n_reads, int64_t* file_bytes);
+/* The 1x chunks of docker/reads2svs.sh:65-74 (N_ROWS_1X = N_ROWS / MAX_COVERAGE, rounded up to a multiple of 4;
+ * `split -d -l`) and the coverage sweep of :98-128 (coverage c = the first c chunks): rows per chunk, rows and bytes
+ * of the prefix of the mixed file that makes up `coverage`. Outputs may be NULL. */
+int sp_reads_mix_coverage_prefix(sp_ctx* ctx, int32_t max_coverage, int32_t coverage, int64_t* n_rows_1x, int64_t* n_rows,
+                                 int64_t* n_bytes);
+/* Bytes [offset, offset+n_bytes) of the mixed file -> host. */
+int sp_reads_mix_copy(sp_ctx* ctx, int64_t offset, int64_t n_bytes, uint8_t* host_out);
+/* Device view: the file bytes and the n_reads+1 byte offsets (int64) of its records. Outputs may be NULL. */
+int sp_reads_mix_device(sp_ctx* ctx, void** file_bytes, void** read_offsets, int64_t* n_reads, int64_t* n_bytes);
+/* The n_reads+1 record offsets -> host. */
+int sp_reads_mix_offsets(sp_ctx* ctx, int64_t* read_offsets);
+/* Device time of the last finish: ordering (keys, sort, scans, segment table) and the tiled copy. */
+int sp_reads_mix_timing(sp_ctx* ctx, double* order_ms, double* copy_ms);
+/* docker/haplotype2reads.sh:53-64 for the individual with haplotypes id1 and id1+1 (sp_reads_configure holds the pbsim
+ * options): materialise both, pbsim on each (ref_num 1, as each is its own process there), mix, write output_file
+ * (NULL = keep it on the device only). */
+int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const char* output_file, int64_t* n_reads,
+                       int64_t* file_bytes);
+
 /* ---- row D: SampleReadsFromLengthBins ------------------------------------------------------------------------------ */
 /* Positional argv of SampleReadsFromLengthBins.main (src/SampleReadsFromLengthBins.java:20-30). args[0..4] (the two
  * normal distributions and the left weight) only feed buildCumulativeBimodal (:87-102), which needs commons-math3's

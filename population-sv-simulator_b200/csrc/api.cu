@@ -9,6 +9,7 @@ void materialise(sp_ctx* c);
 void free_population(sp_ctx* c);
 void free_reads(sp_ctx* c);
 void free_length_bins(sp_ctx* c);
+void free_read_mix(sp_ctx* c);
 
 std::string java_double_to_string(double d) {
     if (d != d) return "NaN";
@@ -226,6 +227,7 @@ void sp_destroy(sp_ctx* ctx) {
     sp::free_population(ctx);
     sp::free_reads(ctx);
     sp::free_length_bins(ctx);
+    sp::free_read_mix(ctx);
     if (ctx->ev_plan) cudaEventDestroy(ctx->ev_plan);
     delete ctx;
     if (s) cudaStreamDestroy(s);

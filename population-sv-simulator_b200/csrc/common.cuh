@@ -14,6 +14,7 @@ namespace sp {
 struct PopulationState;
 struct ReadState;
 struct LengthBinState;
+struct ReadMixState;
 
 struct Error : std::runtime_error {
     int code;
@@ -52,6 +53,7 @@ struct DevBuf {
         if (p) cudaFree(p);
         p = nullptr; cap = 0;
     }
+    void swap(DevBuf& o) { T* tp = p; p = o.p; o.p = tp; size_t tc = cap; cap = o.cap; o.cap = tc; }
     ~DevBuf() { release(); }
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
@@ -133,4 +135,7 @@ struct sp_ctx {
 
     // row D: SampleReadsFromLengthBins
     sp::LengthBinState* bins = nullptr;
+
+    // §8(f) rank 1: the tail of docker/haplotype2reads.sh (cat, shuf, tr) and the coverage chunks of reads2svs.sh
+    sp::ReadMixState* mix = nullptr;
 };

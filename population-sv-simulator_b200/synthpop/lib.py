@@ -114,6 +114,15 @@ def load() -> C.CDLL:
         "sp_set_stream": (C.c_int, [vp, vp]),
         "sp_set_population_stream": (C.c_int, [vp, vp]),
         "sp_kernel_launches": (i64, [vp]),
+        "sp_reads_mix_begin": (C.c_int, [vp]),
+        "sp_reads_mix_add": (C.c_int, [vp]),
+        "sp_reads_mix_finish": (C.c_int, [vp, i64, vp, vp]),
+        "sp_reads_mix_coverage_prefix": (C.c_int, [vp, i32, i32, vp, vp, vp]),
+        "sp_reads_mix_copy": (C.c_int, [vp, i64, i64, vp]),
+        "sp_reads_mix_device": (C.c_int, [vp, vp, vp, vp, vp]),
+        "sp_reads_mix_offsets": (C.c_int, [vp, vp]),
+        "sp_reads_mix_timing": (C.c_int, [vp, vp, vp]),
+        "sp_haplotype2reads": (C.c_int, [vp, i32, i64, cp, vp, vp]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
         "sp_reference_length": (i64, [vp]),
@@ -373,6 +382,44 @@ class Context:
         if ai is not None and ai.size == 0:
             ai = np.zeros(1, dtype=np.int32)
         self._check(self.lib.sp_population_finish(self.h, _ptr(gc), _ptr(ao), _ptr(ai), int(write_joint_outputs)))
+
+    # ---- §8(f) rank 1: haplotype2reads.sh tail (cat, shuf, tr) + reads2svs.sh coverage chunks -------------------------
+    def reads_mix_begin(self):
+        self._check(self.lib.sp_reads_mix_begin(self.h))
+
+    def reads_mix_add(self):
+        self._check(self.lib.sp_reads_mix_add(self.h))
+
+    def reads_mix_finish(self, shuffle_seed: int):
+        n, b = C.c_int64(), C.c_int64()
+        self._check(self.lib.sp_reads_mix_finish(self.h, shuffle_seed, C.byref(n), C.byref(b)))
+        return n.value, b.value
+
+    def reads_mix_coverage_prefix(self, max_coverage: int, coverage: int):
+        a, r, b = C.c_int64(), C.c_int64(), C.c_int64()
+        self._check(self.lib.sp_reads_mix_coverage_prefix(self.h, max_coverage, coverage, C.byref(a), C.byref(r), C.byref(b)))
+        return dict(rows_1x=a.value, rows=r.value, bytes=b.value)
+
+    def reads_mix_copy(self, offset: int, n_bytes: int) -> np.ndarray:
+        out = np.empty(max(n_bytes, 1), dtype=np.uint8)
+        self._check(self.lib.sp_reads_mix_copy(self.h, offset, n_bytes, _ptr(out)))
+        return out[:n_bytes]
+
+    def reads_mix_offsets(self, n_reads: int) -> np.ndarray:
+        out = np.zeros(n_reads + 1, dtype=np.int64)
+        self._check(self.lib.sp_reads_mix_offsets(self.h, _ptr(out)))
+        return out
+
+    def reads_mix_timing(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(self.lib.sp_reads_mix_timing(self.h, C.byref(a), C.byref(b)))
+        return dict(order_ms=a.value, copy_ms=b.value)
+
+    def haplotype2reads(self, id1: int, shuffle_seed: int, output_file: str | None = None):
+        n, b = C.c_int64(), C.c_int64()
+        self._check(self.lib.sp_haplotype2reads(self.h, id1, shuffle_seed, output_file.encode() if output_file else None,
+                                                C.byref(n), C.byref(b)))
+        return n.value, b.value
 
     # ---- row P: reads (pbsim2 model mode) --------------------------------------------------------------------
     def reads_configure(self, args: "ReadArgs"):
