@@ -199,6 +199,18 @@ int sp_reads_device(sp_ctx* ctx, void** records, void** record_offsets, void** d
  * calling script at :54 and is not written.) */
 int sp_simulate_reads(sp_ctx* ctx, const sp_read_args* args, const char* fasta_path);
 
+/* ---- row T (extension): a Mendelian child ------------------------------------------------------------------------ */
+/* Nothing in the reference derives a child (its trios are real families, src/GetTrioChildren.java:5-17), so this row
+ * has no reference arithmetic to match; it is defined here. After sp_population_finish: the child
+ * of individuals `father` and `mother` inherits one whole haplotype from each (no recombination), chosen by one
+ * nextBoolean() per parent from java.util.Random(seed), father first: child haplotype 0 = haplotype 2*father + b_f,
+ * child haplotype 1 = haplotype 2*mother + b_m. The two lists are appended to the context as haplotypes H and H+1
+ * (returned in child_first_haplotype), so sp_plan_haplotypes / sp_materialise / sp_haplotype2reads apply unchanged and a
+ * child can be a parent in turn. write_vcf != 0 writes OUTPUT_DIR/groundTruth_individual_<H>.vcf with the reference's
+ * own buildVCF merge (src/SimulateHaplotypes.java:1027-1066). Outputs may be NULL. */
+int sp_trio_add_child(sp_ctx* ctx, int32_t father_individual, int32_t mother_individual, int64_t seed, int32_t write_vcf,
+                      int32_t* child_first_haplotype, int32_t* from_father_haplotype, int32_t* from_mother_haplotype);
+
 /* ---- the tail of docker/haplotype2reads.sh and the coverage chunks of reads2svs.sh ------- */
 /* `cat reads_ID2.fa >> reads_ID1.fa; shuf; tr 'Z' '\n'` (docker/haplotype2reads.sh:59-63) on the device.
  * begin: start a new individual. add: take the records of the last sp_reads_simulate_* call (ownership of the device

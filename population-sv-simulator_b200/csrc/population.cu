@@ -90,7 +90,19 @@ void population_begin(sp_ctx* c, const sp_population_args* a, int32_t first_h, i
         P.h_thr[v] = t;
     }
     run_genotype_and_collisions(c, P);                                  // :104 (loops A and the collision fixer)
-    P.begun = true;
+    P.begun = true; P.finished = false;
+}
+
+static void upload_context_lists(sp_ctx* c) {
+    const int32_t H = c->n_haplotypes;
+    c->d_list_off.reserve(H + 1);
+    c->d_list_ids.reserve(std::max<size_t>(c->h_list_ids.size(), 1));
+    SP_CUDA(cudaMemcpyAsync(c->d_list_off.p, c->h_list_off.data(), ((size_t)H + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    if (!c->h_list_ids.empty())
+        SP_CUDA(cudaMemcpyAsync(c->d_list_ids.p, c->h_list_ids.data(), c->h_list_ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    SP_CUDA(cudaStreamSynchronize(c->stream));
+    c->view_own_lists();
+    c->plan_last = -1; c->plan_first = 0;
 }
 
 void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* all_off, const int32_t* all_ids, int32_t write_joint) {
@@ -142,13 +154,40 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
         }
         c->h_list_ids = P.h_ids;
     }
-    c->d_list_off.reserve(H + 1);
-    c->d_list_ids.reserve(std::max<size_t>(c->h_list_ids.size(), 1));
-    SP_CUDA(cudaMemcpyAsync(c->d_list_off.p, c->h_list_off.data(), ((size_t)H + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-    if (!c->h_list_ids.empty())
-        SP_CUDA(cudaMemcpyAsync(c->d_list_ids.p, c->h_list_ids.data(), c->h_list_ids.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    SP_CUDA(cudaStreamSynchronize(c->stream));
-    c->view_own_lists();
+    upload_context_lists(c);
+    P.finished = true;
+}
+
+// Row T of SURVEY.md §8a (an EXTENSION: the reference's trios are real families, src/GetTrioChildren.java:5-17; no code
+// there derives a child). The child of individuals `father` and `mother` inherits one whole haplotype from each parent
+// (no recombination), chosen by one nextBoolean() per parent from java.util.Random(seed) — father first. Its two
+// haplotypes are appended to the context's lists as haplotypes H and H+1 (so sp_plan_haplotypes / sp_materialise /
+// sp_haplotype2reads work on them unchanged, and a child can be a parent in turn) and its truth VCF is the same
+// buildVCF merge (:1027-1066) the reference applies to every individual.
+void trio_add_child(sp_ctx* c, int32_t father, int32_t mother, int64_t seed, int32_t write_vcf, int32_t* child_first,
+                    int32_t* from_father, int32_t* from_mother) {
+    if (!c->pop || !c->pop->finished) throw Error(SP_ERR_ARG, "sp_population_finish has not been called");
+    PopulationState& P = *c->pop;
+    const int32_t H = c->n_haplotypes;
+    if (father < 0 || mother < 0 || 2 * father + 1 >= H || 2 * mother + 1 >= H)
+        throw Error(SP_ERR_JAVA_EXCEPTION, "ArrayIndexOutOfBoundsException: parent individual outside [0," + std::to_string(H / 2) + ")");
+    auto local = [&](int32_t ind) { return P.have_all_lists || ind >= P.n_haplotypes_total / 2 || (2 * ind >= P.h0 && 2 * ind + 1 < P.h1); };
+    if (!local(father) || !local(mother)) throw Error(SP_ERR_ARG, "trio: the parents' haplotype lists are not on this rank");
+    JavaRandom rng(seed);
+    const int32_t hf = 2 * father + (rng.nextBoolean() ? 1 : 0);
+    const int32_t hm = 2 * mother + (rng.nextBoolean() ? 1 : 0);
+    for (int32_t h : {hf, hm}) {
+        const int64_t a = c->h_list_off[h], b = c->h_list_off[h + 1];
+        c->h_list_ids.reserve(c->h_list_ids.size() + (size_t)(b - a));
+        for (int64_t k = a; k < b; k++) c->h_list_ids.push_back(c->h_list_ids[(size_t)k]);
+        c->h_list_off.push_back((int64_t)c->h_list_ids.size());
+    }
+    c->n_haplotypes = H + 2;
+    upload_context_lists(c);
+    if (write_vcf) write_individual_vcfs(P, c->h_ref.data(), (int32_t)c->ref_len, H, H + 1, c->h_list_off.data(), c->h_list_ids.data(), 0);
+    if (child_first) *child_first = H;
+    if (from_father) *from_father = hf;
+    if (from_mother) *from_mother = hm;
 }
 
 // Rows G/C/N again for haplotypes [first..last] with the model, variants and thresholds already resident; the
@@ -250,6 +289,14 @@ int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, i
     sp::PopulationState& P = pop_of(ctx);
     if (steps_after_sample_variants) *steps_after_sample_variants = P.steps_after_sampling;
     if (candidates) *candidates = P.candidates;
+    SP_API_END
+}
+
+int sp_trio_add_child(sp_ctx* ctx, int32_t father_individual, int32_t mother_individual, int64_t seed, int32_t write_vcf,
+                      int32_t* child_first_haplotype, int32_t* from_father_haplotype, int32_t* from_mother_haplotype) {
+    SP_API_BEGIN
+    sp::trio_add_child(ctx, father_individual, mother_individual, seed, write_vcf, child_first_haplotype,
+                       from_father_haplotype, from_mother_haplotype);
     SP_API_END
 }
 

@@ -60,7 +60,7 @@ struct PopulationState {
     std::vector<int64_t> all_off;         // CSR over ALL haplotypes (only where the joint outputs are written)
     std::vector<int32_t> all_ids;
     bool have_all_lists = false;
-    bool begun = false;
+    bool begun = false, finished = false;
 };
 
 void run_genotype_and_collisions(sp_ctx* c, PopulationState& P);

@@ -114,6 +114,7 @@ def load() -> C.CDLL:
         "sp_set_stream": (C.c_int, [vp, vp]),
         "sp_set_population_stream": (C.c_int, [vp, vp]),
         "sp_kernel_launches": (i64, [vp]),
+        "sp_trio_add_child": (C.c_int, [vp, i32, i32, i64, i32, vp, vp, vp]),
         "sp_reads_mix_begin": (C.c_int, [vp]),
         "sp_reads_mix_add": (C.c_int, [vp]),
         "sp_reads_mix_finish": (C.c_int, [vp, i64, vp, vp]),
@@ -382,6 +383,13 @@ class Context:
         if ai is not None and ai.size == 0:
             ai = np.zeros(1, dtype=np.int32)
         self._check(self.lib.sp_population_finish(self.h, _ptr(gc), _ptr(ao), _ptr(ai), int(write_joint_outputs)))
+
+    # ---- row T (extension): Mendelian child -----------------------------------------------------------------------
+    def trio_add_child(self, father_individual: int, mother_individual: int, seed: int, write_vcf: bool = True):
+        h, f, m = C.c_int32(), C.c_int32(), C.c_int32()
+        self._check(self.lib.sp_trio_add_child(self.h, father_individual, mother_individual, seed, int(write_vcf),
+                                               C.byref(h), C.byref(f), C.byref(m)))
+        return dict(child_first_haplotype=h.value, from_father_haplotype=f.value, from_mother_haplotype=m.value)
 
     # ---- §8(f) rank 1: haplotype2reads.sh tail (cat, shuf, tr) + reads2svs.sh coverage chunks -------------------------
     def reads_mix_begin(self):
