@@ -40,6 +40,17 @@ def measured_peak_gbs():
     return 6650.0, "fallback"
 
 
+def measured_traffic(batch: int, L: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one materialise_kernel launch, from the committed `ncu --set full`
+    capture (profiles/r01_traffic.json); only quoted when this run's launch has the captured shape."""
+    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(p):
+        t = json.load(open(p))
+        if t.get("batch") == batch and t.get("reference_length") == L:
+            return t["dram_bytes_per_launch"]
+    return None
+
+
 def synth_population(L: int, H: int, seed: int = 20261104):
     """Synthetic variant table + per-haplotype edit lists of the shape SimulateHaplotypes produces
     (V ~ 11k SVs, ~1.1k per haplotype, type mix DEL .52 / DUP .15 / INS .328 / INV .002, globally non-overlapping so
@@ -92,15 +103,35 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
     t0 = time.perf_counter()
     bases = reads = dropped = 0
     k_ms = p_ms = 0.0
+    mix = n_haps == 2   # an individual: the two haplotypes' reads are shuffled into one file on the device
+    used = None
+    if mix:
+        ctx.reads_mix_begin()
     for h in range(first_hap, first_hap + n_haps):
-        r = ctx.reads_simulate_haplotype(h, h + 1)
+        r = ctx.reads_simulate_haplotype(h, 1 if mix else h + 1)
         tm = ctx.reads_timing()
         bases += r["bases"]; reads += r["n_reads"]; dropped += r["n_dropped"]
         k_ms += tm["kernel_ms"]; p_ms += tm["plan_ms"]
+        if h == first_hap + n_haps - 1:
+            _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of the last haplotype's reads
+        if mix:
+            ctx.reads_mix_add()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of the last haplotype's reads
     draws_per_base = float(used.astype(np.int64).sum()) / max(1, r["bases"])
+    mix_obj = None
+    if mix:
+        # docker/haplotype2reads.sh:59-63 (cat, shuf, tr) and the 10x/20x/30x prefixes of reads2svs.sh:65-128
+        t1 = time.perf_counter()
+        n_mixed, mixed_bytes = ctx.reads_mix_finish(42)
+        torch.cuda.synchronize()
+        t_mix = time.perf_counter() - t1
+        mt = ctx.reads_mix_timing()
+        sweep = {f"{c}x": ctx.reads_mix_coverage_prefix(depth, c)["bytes"] for c in sorted({max(1, depth // 3), max(1, 2 * depth // 3), depth})}
+        mix_obj = {"what": "cat + seeded shuf + tr 'Z' '\\n' of the individual's reads on the device, coverage prefixes as byte ranges",
+                   "reads": n_mixed, "file_bytes": mixed_bytes, "wall_s": t_mix, "order_ms": mt["order_ms"], "copy_ms": mt["copy_ms"],
+                   "copy_GBps_algorithmic": 2.0 * mixed_bytes / (mt["copy_ms"] / 1e3) / 1e9, "copy_frac_of_peak": 2.0 * mixed_bytes / (mt["copy_ms"] / 1e3) / 1e9 / peak,
+                   "coverage_prefix_bytes": sweep}
     achieved = READ_ALGO_BYTES_PER_BASE * bases / (k_ms / 1e3) / 1e9
     return {"metric": "CCS read Gbp/s", "value": bases / dt / 1e9, "unit": "Gbp/s",
             "workload": f"pbsim2 model mode, {depth}x over {n_haps} materialised chr1-sized haplotypes, length 15000+-2000 in [5000,30000], "
@@ -109,7 +140,8 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
             "reads": reads, "dropped_NNNNN": dropped, "bases": bases, "wall_s": dt, "kernel_ms": k_ms, "host_plan_ms": p_ms,
             "kernel_gbp_s": bases / (k_ms / 1e3) / 1e9, "gpu_launches": ctx.kernel_launches - l0,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE}}
+                         "traffic": None, "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE},
+            "mix": mix_obj}
 
 
 def reads_cpu_baseline(synth, work, L=1_500_000, depth=30):
@@ -143,6 +175,27 @@ class ClockSampler(threading.Thread):
         self.stop_flag = False
 
     def run(self):
+        try:   # NVML in-process: a sample every 20 ms (nvidia-smi takes ~0.4 s per call on these boxes)
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            bits = [(getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8), 2), (getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40), 3),
+                    (getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20), 4), (getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4), 5)]
+            while not self.stop_flag:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                row = [str(sm), str(mx), "", "", "", ""]
+                for bit, col in bits:
+                    row[col] = "Active" if (r & bit) else "Not Active"
+                self.rows.append(row)
+                time.sleep(0.02)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         while not self.stop_flag:
@@ -184,6 +237,18 @@ def cpu_baseline_sample(ref, pop, budget_s: float = 12.0, max_haps: int = 64):
     return bases / dt / 1e9, n, dt
 
 
+_REF_ARM = None
+
+
+def _ref_arm_one(h):
+    """one haplotype of the reference arm in a forked worker (the arrays are inherited, not pickled)"""
+    import oracle_helpers as oh
+    ref, pop = _REF_ARM
+    out = oh.build_haplotype(oh.load_oracle(), ref, pop["sv_type"], pop["position"], pop["length"], pop["payload_off"],
+                             pop["payload"], None, pop["lists"][h])
+    return int(out.size)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -209,33 +274,33 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
+        # The reference path is single-threaded by construction (one JVM per individual, wdl/SimulateHaplotypes.wdl:263);
+        # "all the host threads it can use" = one process per core, each building whole haplotypes, as the WDL scatter does.
+        import multiprocessing as mp
+        cores = len(os.sched_getaffinity(0))
         ref = random_reference(L)
-        pop = synth_population(L, max(64, args.batch))
-        vals = []
-        per = max(1, min(8, 64 // max(1, args.steps + args.warmup)))
-        import oracle_helpers as oh
-        olib = oh.load_oracle()
-        h = 0
-        t_all = []
-        for s in range(args.warmup + args.steps):
-            t0 = time.perf_counter()
-            bases = 0
-            for _ in range(per):
-                out = oh.build_haplotype(olib, ref, pop["sv_type"], pop["position"], pop["length"], pop["payload_off"],
-                                         pop["payload"], None, pop["lists"][h % len(pop["lists"])])
-                bases += out.size
-                h += 1
-            dt = time.perf_counter() - t0
-            if s >= args.warmup:
-                vals.append(bases / dt / 1e9)
-                t_all.append(dt)
+        pop = synth_population(L, max(64, cores))
+        global _REF_ARM
+        _REF_ARM = (ref, pop)
+        vals, t_all = [], []
+        with mp.get_context("fork").Pool(cores) as pool:
+            h = 0
+            for s in range(args.warmup + args.steps):
+                t0 = time.perf_counter()
+                bases = sum(pool.map(_ref_arm_one, [(h + k) % len(pop["lists"]) for k in range(cores)], chunksize=1))
+                h += cores
+                dt = time.perf_counter() - t0
+                if s >= args.warmup:
+                    vals.append(bases / dt / 1e9)
+                    t_all.append(dt)
         v = float(np.mean(vals))
         line = {"metric": "simulated haplotype Gbp/s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(t_all)), "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
                 "config": {"workload": workload, "l2": "inputs larger than L2"},
-                "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": 1, "kind": "port",
-                                 "sample": f"{per} haplotypes per step (CPU restatement of buildHaplotypes, single thread; no JVM in this image)"},
+                "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": cores, "kind": "port",
+                                 "sample": f"{cores} chr1-sized haplotypes per step, one process per host core (CPU restatement of "
+                                           f"buildHaplotypes; the reference is Java and no JVM exists in this image)"},
                 "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return
@@ -384,7 +449,7 @@ def main():
                            "l2": "inputs larger than L2 (>=31 GB written per step)", "sharding": "by individual, no collective"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "materialise_kernel", "peak_kind": peak_kind,
+                             "traffic": measured_traffic(args.batch, L), "kernel": "materialise_kernel", "peak_kind": peak_kind,
                              "algorithmic_bytes_per_bp": ALGO_BYTES_PER_BP, "kernel_ms_per_step": 1e3 * t_kernel / args.steps,
                              "genotype_call_ms_per_step": 1e3 * t_geno / args.steps, "plan_ms_per_step": 1e3 * t_plan / args.steps},
                 "setup_s": {"generate_inputs": round(t_gen, 2), "simulate_population_once": round(t_pop, 2)},

@@ -67,6 +67,14 @@ constexpr int64_t SEG_OFF_MASK = (int64_t(1) << 48) - 1;
 
 constexpr int TILE_BYTES = 16384;  // output bytes per CTA tile of the materialisation kernel
 
+// Per-tile descriptor written by tile_table_kernel. nseg == 0: the tile lies inside one forward segment and srcw holds
+// its kind (bits 62..60) and the source byte offset of the tile's first byte; otherwise segments [s0, s0+nseg) of the
+// slot intersect the tile.
+struct alignas(16) TileDesc {
+    int64_t srcw;
+    int32_t s0, nseg;
+};
+
 }  // namespace sp
 
 struct sp_ctx {
@@ -120,7 +128,7 @@ struct sp_ctx {
     std::vector<int64_t> h_hap_len;      // framed lengths
     std::vector<int32_t> h_hdr_len;      // header bytes preceding the sequence in each slot
     sp::DevBuf<int64_t> d_seg_dst, d_seg_src, d_seg_base, d_hap_len;
-    sp::DevBuf<int32_t> d_tile_first;
+    sp::DevBuf<sp::TileDesc> d_tile_desc;
     sp::DevBuf<uint8_t> d_aux;
     sp::DevBuf<int64_t> d_aux_off;
     sp::DevBuf<int32_t> d_err;

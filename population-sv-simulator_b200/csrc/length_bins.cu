@@ -23,7 +23,7 @@
 namespace sp {
 
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, int32_t* tile_first, uint8_t* out, int64_t stride,
+                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
                        int n_slots);
 
 constexpr int LB_CTA = 256;  // attempts per CTA
@@ -43,7 +43,7 @@ struct LengthBinState {
     DevBuf<int32_t> d_bin, d_rec, d_hist_blocks, d_hist;
     DevBuf<int64_t> d_block_sums, d_acc_incl, d_cov_incl, d_bytes_excl, d_result;
     DevBuf<int64_t> d_seg_dst, d_seg_src, d_seg_base;
-    DevBuf<int32_t> d_tile_first;
+    DevBuf<TileDesc> d_tile_first;
     DevBuf<uint8_t> d_hdr, d_out;
     int64_t n_reads = 0, out_bytes = 0, attempts = 0, coverage = 0;
     std::vector<int32_t> h_hist;

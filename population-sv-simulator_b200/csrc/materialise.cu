@@ -138,20 +138,42 @@ plan_kernel(const int8_t* __restrict__ type, const int32_t* __restrict__ pos, co
     }
 }
 
+// One thread per 16 KiB output tile: which segments intersect it, and — for the common tile that lies inside one
+// forward segment — where its source bytes start, so that the copy kernel needs ONE 16-byte descriptor load before its
+// data loads instead of a chain through tile_first -> seg_dst/seg_src.
 __global__ void __launch_bounds__(256)
-tile_table_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict__ seg_base, int n_hap,
-                  int64_t tiles_per_slot, int32_t* __restrict__ tile_first) {
+tile_table_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
+                  int n_hap, int64_t tiles_per_slot, TileDesc* __restrict__ desc) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= tiles_per_slot * n_hap) return;
     const int hb = (int)(idx / tiles_per_slot);
     const int64_t x = (idx % tiles_per_slot) * TILE_BYTES;
     const int64_t sb = seg_base[hb];
-    int64_t lo = 0, hi = seg_base[hb + 1] - sb;  // first local index with dst > x
+    const int64_t n = seg_base[hb + 1] - sb;  // includes the PAD segment and the INT64_MAX sentinel
+    int64_t lo = 0, hi = n;                   // first local index with dst > x
     while (lo < hi) {
         const int64_t mid = (lo + hi) >> 1;
         if (seg_dst[sb + mid] <= x) lo = mid + 1; else hi = mid;
     }
-    tile_first[idx] = (int32_t)(lo - 1);
+    const int64_t s0 = lo - 1;
+    int64_t lo2 = lo, hi2 = n;                // first local index with dst >= x + TILE_BYTES (the sentinel at the latest)
+    while (lo2 < hi2) {
+        const int64_t mid = (lo2 + hi2) >> 1;
+        if (seg_dst[sb + mid] < x + TILE_BYTES) lo2 = mid + 1; else hi2 = mid;
+    }
+    const int64_t s1 = lo2 - 1;
+    const int64_t src = seg_src[sb + s0];
+    const int kind = (int)(src >> SEG_KIND_SHIFT);
+    TileDesc d;
+    d.s0 = (int32_t)s0;
+    if (s1 == s0 && kind != SEG_REF_RC) {
+        d.nseg = 0;  // uniform tile
+        d.srcw = (int64_t(kind) << SEG_KIND_SHIFT) | (((src & SEG_OFF_MASK) + (x - seg_dst[sb + s0])) & SEG_OFF_MASK);
+    } else {
+        d.nseg = (int32_t)(s1 - s0 + 1);
+        d.srcw = 0;
+    }
+    desc[idx] = d;
 }
 
 __device__ __forceinline__ uint4 shift_combine(uint4 A, uint4 B, unsigned m) {
@@ -167,131 +189,190 @@ __device__ __forceinline__ uint4 shift_combine(uint4 A, uint4 B, unsigned m) {
                       __funnelshift_r(x3, x4, s));
 }
 
-// 16 bytes starting at an arbitrary address (buffers carry >= 32 bytes of slack past their end).
-__device__ __forceinline__ uint4 load16_any(const uint8_t* p) {
-    const uintptr_t a = (uintptr_t)p;
-    const unsigned m = (unsigned)(a & 15u);
-    const uint4* q = (const uint4*)(a - m);
-    const uint4 A = __ldg(q);
-    if (m == 0) return A;
-    const uint4 B = __ldg(q + 1);
-    return shift_combine(A, B, m);
+constexpr int MAX_TILE_SEGS = 96;
+constexpr int COUNT_SEARCH_SEGS = 12;  // up to here the segment of a chunk is found by counting (independent loads)
+
+// Tile with more than MAX_TILE_SEGS segments (thousands of tiny records): rare, kept simple. One 16-byte chunk at a
+// time, segment found by binary search in global memory, bytes gathered one by one.
+__device__ __noinline__ void copy_tile_many_segments(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload,
+                                                     const uint8_t* __restrict__ aux, const int64_t* __restrict__ gd,
+                                                     const int64_t* __restrict__ gs, int nseg, int64_t x0,
+                                                     uint8_t* __restrict__ dst_tile) {
+    for (int c = threadIdx.x; c < TILE_BYTES / 16; c += 256) {
+        const int64_t x = x0 + (int64_t)c * 16;
+        int i = 0, hi = nseg;  // last i in [0,nseg) with gd[i] <= x
+        while (hi - i > 1) {
+            const int mid = (i + hi) >> 1;
+            if (gd[mid] <= x) i = mid; else hi = mid;
+        }
+        int64_t dcur = gd[i], dnext = gd[i + 1], src = gs[i];
+        uint32_t w[4] = {0, 0, 0, 0};
+        bool any = false;
+#pragma unroll 1
+        for (int j = 0; j < 16; j++) {
+            const int64_t xb = x + j;
+            while (xb >= dnext) { i++; dcur = dnext; dnext = gd[i + 1]; src = gs[i]; }
+            const int kind = (int)(src >> SEG_KIND_SHIFT);
+            const int64_t o = src & SEG_OFF_MASK, r = xb - dcur;
+            uint8_t byte = 0;
+            if (kind == SEG_REF_FWD) byte = ref[o + r];
+            else if (kind == SEG_REF_RC) byte = complement_base(ref[o - r]);
+            else if (kind == SEG_PAYLOAD) byte = payload[o + r];
+            else if (kind == SEG_AUX) byte = aux[o + r];
+            if (kind != SEG_PAD) any = true;
+            w[j >> 2] |= (uint32_t)byte << ((j & 3) * 8);
+        }
+        if (any) __stcs((uint4*)(dst_tile + (int64_t)c * 16), make_uint4(w[0], w[1], w[2], w[3]));
+    }
 }
 
-constexpr int MAX_TILE_SEGS = 96;
-
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
 materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload,
                    const uint8_t* __restrict__ aux, const int64_t* __restrict__ seg_dst,
                    const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
-                   const int32_t* __restrict__ tile_first, uint8_t* __restrict__ out, int64_t stride,
+                   const TileDesc* __restrict__ desc, uint8_t* __restrict__ out, int64_t stride,
                    int64_t tiles_per_slot, int n_hap) {
     // region-major order: consecutive CTAs work on the same tile index of different haplotypes
     const int64_t b = blockIdx.x;
     const int hb = (int)(b % n_hap);
     const int64_t t = b / n_hap;
     const int64_t x0 = t * TILE_BYTES;
-    const int64_t sb = seg_base[hb];
-    const int64_t ti = (int64_t)hb * tiles_per_slot + t;
-    const int s0 = tile_first[ti];
-    const int s_last = (int)(seg_base[hb + 1] - sb) - 2;  // the PAD segment
-    int s1 = (t + 1 < tiles_per_slot) ? tile_first[ti + 1] : s_last;
-    if (s1 > s_last) s1 = s_last;
+    const int4 dw = __ldg((const int4*)(desc + ((int64_t)hb * tiles_per_slot + t)));
     uint8_t* __restrict__ dst_tile = out + (int64_t)hb * stride + x0;
     const int tid = threadIdx.x;
+    constexpr int CH = TILE_BYTES / 16 / 256;
+    const int nseg = dw.w;
 
-    // does segment s1 start at or beyond the end of this tile? then it does not intersect it
-    const int64_t d0 = seg_dst[sb + s0];
-    const int64_t src0 = seg_src[sb + s0];
-    const int64_t d1 = seg_dst[sb + s0 + 1];
-    if (d1 >= x0 + TILE_BYTES) {
-        // ---- uniform path: the whole tile lies inside one segment
-        const int kind = (int)(src0 >> SEG_KIND_SHIFT);
-        const int64_t off = (src0 & SEG_OFF_MASK) + (x0 - d0);
+    if (nseg == 0) {
+        // ---- uniform path: the whole tile lies inside one forward segment
+        const int64_t srcw = ((int64_t)(uint32_t)dw.y << 32) | (uint32_t)dw.x;
+        const int kind = (int)(srcw >> SEG_KIND_SHIFT);
         if (kind == SEG_PAD) return;
-        if (kind != SEG_REF_RC) {
-            const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
-            const uint8_t* p = base + off;
-            const unsigned m = (unsigned)((uintptr_t)p & 15u);
-            const uint4* q = (const uint4*)(p - m);
-            uint4* o = (uint4*)dst_tile;
-            if (m == 0) {
-                uint4 v[4];
+        const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
+        const uint8_t* p = base + (srcw & SEG_OFF_MASK);
+        const unsigned m = (unsigned)((uintptr_t)p & 15u);
+        const uint4* q = (const uint4*)(p - m);
+        uint4* o = (uint4*)dst_tile;
+        if (m == 0) {
+            uint4 v[CH];
 #pragma unroll
-                for (int u = 0; u < 4; u++) v[u] = __ldg(q + u * 256 + tid);
+            for (int u = 0; u < CH; u++) v[u] = __ldg(q + u * 256 + tid);
 #pragma unroll
-                for (int u = 0; u < 4; u++) __stcs(o + u * 256 + tid, v[u]);
-            } else {
-                uint4 A[4], B[4];
+            for (int u = 0; u < CH; u++) __stcs(o + u * 256 + tid, v[u]);
+        } else {
+            uint4 A[CH], B[CH];
 #pragma unroll
-                for (int u = 0; u < 4; u++) { A[u] = __ldg(q + u * 256 + tid); B[u] = __ldg(q + u * 256 + tid + 1); }
+            for (int u = 0; u < CH; u++) { A[u] = __ldg(q + u * 256 + tid); B[u] = __ldg(q + u * 256 + tid + 1); }
 #pragma unroll
-                for (int u = 0; u < 4; u++) __stcs(o + u * 256 + tid, shift_combine(A[u], B[u], m));
-            }
-            return;
+            for (int u = 0; u < CH; u++) __stcs(o + u * 256 + tid, shift_combine(A[u], B[u], m));
         }
+        return;
     }
 
     // ---- general path: several segments (or a reverse-complemented one) intersect the tile
-    __shared__ int64_t s_dst[MAX_TILE_SEGS + 1];
-    __shared__ int64_t s_src[MAX_TILE_SEGS];
-    const int nseg = s1 - s0 + 1;
-    const bool in_smem = nseg <= MAX_TILE_SEGS;
-    if (in_smem) {
-        for (int i = tid; i <= nseg; i += 256) s_dst[i] = seg_dst[sb + s0 + i];
-        for (int i = tid; i < nseg; i += 256) s_src[i] = seg_src[sb + s0 + i];
+    const int64_t sb = seg_base[hb] + dw.z;
+    if (nseg > MAX_TILE_SEGS) {
+        copy_tile_many_segments(ref, payload, aux, seg_dst + sb, seg_src + sb, nseg, x0, dst_tile);
+        return;
+    }
+    // Segment table of the tile in shared memory, relative to the tile: rel[i] = first output byte of segment i minus x0
+    // (clamped to 32 bits), adj[i] = source offset that corresponds to x0 (forward: src + (x - x0), reverse
+    // complement: src - (x - x0)), kind[i].
+    __shared__ int32_t s_rel[MAX_TILE_SEGS + 1];
+    __shared__ int64_t s_adj[MAX_TILE_SEGS];
+    __shared__ int32_t s_kind[MAX_TILE_SEGS];
+    for (int i = tid; i <= nseg; i += 256) {
+        const int64_t r = seg_dst[sb + i] - x0;
+        s_rel[i] = (int32_t)(r < -(1 << 30) ? -(1 << 30) : (r > (1 << 30) ? (1 << 30) : r));
+        if (i < nseg) {
+            const int64_t src = seg_src[sb + i];
+            const int kind = (int)(src >> SEG_KIND_SHIFT);
+            s_kind[i] = kind;
+            s_adj[i] = kind == SEG_REF_RC ? (src & SEG_OFF_MASK) + r : (src & SEG_OFF_MASK) - r;
+        }
     }
     __syncthreads();
-    const int64_t* gd = seg_dst + sb + s0;
-    const int64_t* gs = seg_src + sb + s0;
-    auto DST = [&](int i) -> int64_t { return in_smem ? s_dst[i] : gd[i]; };
-    auto SRC = [&](int i) -> int64_t { return in_smem ? s_src[i] : gs[i]; };
-    for (int c = tid; c < TILE_BYTES / 16; c += 256) {
-        const int64_t x = x0 + (int64_t)c * 16;
-        int lo = 0, hi = nseg;  // last i in [0,nseg) with DST(i) <= x   (DST(0) <= x0 always)
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (DST(mid) <= x) lo = mid; else hi = mid;
-        }
-        int i = lo;
-        int64_t src = SRC(i);
-        int kind = (int)(src >> SEG_KIND_SHIFT);
-        int64_t dnext = DST(i + 1);
-        uint4 v;
-        if (x + 16 <= dnext && kind != SEG_REF_RC) {
-            if (kind == SEG_PAD) continue;
-            const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
-            v = load16_any(base + (src & SEG_OFF_MASK) + (x - DST(i)));
+    auto find_segment = [&](int xr) -> int {  // last i in [0,nseg) with rel[i] <= xr (rel[0] <= 0 always)
+        int lo = 0;
+        if (nseg <= COUNT_SEARCH_SEGS) {
+            for (int i = 1; i < nseg; i++) lo += s_rel[i] <= xr ? 1 : 0;
         } else {
-            uint32_t w[4] = {0, 0, 0, 0};
-            int64_t dcur = DST(i);
-            bool any = false;
-#pragma unroll 1
-            for (int j = 0; j < 16; j++) {
-                const int64_t xb = x + j;
-                while (xb >= dnext) {  // zero-length segments are skipped here as well
-                    i++;
-                    dcur = dnext; dnext = DST(i + 1); src = SRC(i);
-                    kind = (int)(src >> SEG_KIND_SHIFT);
-                }
-                uint8_t byte = 0;
-                const int64_t o = (src & SEG_OFF_MASK);
-                if (kind == SEG_REF_FWD) byte = ref[o + (xb - dcur)];
-                else if (kind == SEG_REF_RC) byte = complement_base(ref[o - (xb - dcur)]);
-                else if (kind == SEG_PAYLOAD) byte = payload[o + (xb - dcur)];
-                else if (kind == SEG_AUX) byte = aux[o + (xb - dcur)];
-                if (kind != SEG_PAD) any = true;
-                w[j >> 2] |= (uint32_t)byte << ((j & 3) * 8);
+            int hi = nseg;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (s_rel[mid] <= xr) lo = mid; else hi = mid;
             }
-            if (!any) continue;
-            v = make_uint4(w[0], w[1], w[2], w[3]);
         }
-        __stcs((uint4*)(dst_tile + (int64_t)c * 16), v);
+        return lo;
+    };
+    // Phase 1: every thread resolves its four 16-byte chunks and issues the loads of all the chunks that lie inside one
+    // forward segment (8 aligned 16-byte loads in flight per thread, as in the uniform path). Phase 2: realign + store.
+    // Phase 3: the few chunks that straddle a segment boundary or belong to a reverse-complemented segment: sixteen
+    // independent byte loads each.
+    uint4 A[CH], B[CH];
+    unsigned mis[CH];
+    unsigned vec_mask = 0, slow_mask = 0;
+#pragma unroll
+    for (int u = 0; u < CH; u++) {
+        const int xr = (tid + u * 256) * 16;
+        const int lo = find_segment(xr);
+        const int kind = s_kind[lo];
+        mis[u] = 0;
+        if (xr + 16 > s_rel[lo + 1] || kind == SEG_REF_RC) slow_mask |= 1u << u;
+        else if (kind != SEG_PAD) {
+            const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
+            const uint8_t* p = base + (s_adj[lo] + xr);
+            const unsigned m = (unsigned)((uintptr_t)p & 15u);
+            const uint4* q = (const uint4*)(p - m);
+            A[u] = __ldg(q);
+            B[u] = __ldg(q + 1);   // buffers carry >= 32 bytes of slack past their end
+            mis[u] = m; vec_mask |= 1u << u;
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < CH; u++)
+        if ((vec_mask >> u) & 1u) __stcs((uint4*)(dst_tile + (tid + u * 256) * 16), shift_combine(A[u], B[u], mis[u]));
+#pragma unroll 1
+    for (int u = 0; u < CH; u++) {
+        if (!((slow_mask >> u) & 1u)) continue;
+        const int xr = (tid + u * 256) * 16;
+        int i = find_segment(xr);
+        int rnext = s_rel[i + 1], kind = s_kind[i];
+        int64_t adj = s_adj[i];
+        uint8_t by[16];
+        unsigned rc_mask = 0, any_mask = 0;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const int xb = xr + j;
+            while (xb >= rnext) {  // zero-length segments are skipped here as well
+                i++;
+                rnext = s_rel[i + 1]; kind = s_kind[i]; adj = s_adj[i];
+            }
+            const uint8_t* p = kind == SEG_REF_RC ? ref + (adj - xb)
+                                                  : (kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux)) + (adj + xb);
+            by[j] = 0;
+            if (kind != SEG_PAD) { by[j] = __ldg(p); any_mask |= 1u << j; }
+            if (kind == SEG_REF_RC) rc_mask |= 1u << j;
+        }
+        if (!any_mask) continue;
+        uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const uint8_t byte = (rc_mask >> j) & 1u ? complement_base(by[j]) : by[j];
+            w[j >> 2] |= (uint32_t)byte << ((j & 3) * 8);
+        }
+        __stcs((uint4*)(dst_tile + (tid + u * 256) * 16), make_uint4(w[0], w[1], w[2], w[3]));
     }
 }
 
 // ------------------------------------------------------------------------------------------------- host
 static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+static void launch_materialise(cudaStream_t st, int64_t ntiles, const uint8_t* ref, const uint8_t* payload, const uint8_t* aux,
+                               const int64_t* seg_dst, const int64_t* seg_src, const int64_t* seg_base, const TileDesc* desc,
+                               uint8_t* out, int64_t stride, int64_t tiles_per_slot, int n_slots) {
+    materialise_kernel<<<(unsigned)ntiles, 256, 0, st>>>(ref, payload, aux, seg_dst, seg_src, seg_base, desc, out, stride, tiles_per_slot, n_slots);
+}
 
 void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride) {
     if (c->ref_len <= 0) throw Error(SP_ERR_ARG, "no reference loaded");
@@ -353,9 +434,9 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
     c->tiles_per_slot = c->slot_stride / TILE_BYTES;
     const int64_t ntiles = c->tiles_per_slot * nh;
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "batch too large: reduce the haplotype range");
-    c->d_tile_first.reserve(ntiles);
-    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(c->d_seg_dst.p, c->d_seg_base.p, nh,
-                                                                        c->tiles_per_slot, c->d_tile_first.p);
+    c->d_tile_desc.reserve(ntiles);
+    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(c->d_seg_dst.p, c->d_seg_src.p, c->d_seg_base.p, nh,
+                                                                        c->tiles_per_slot, c->d_tile_desc.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     c->d_out.reserve((size_t)c->slot_stride * nh, 0.01);
@@ -368,9 +449,8 @@ void materialise(sp_ctx* c) {
     if (c->plan_last < c->plan_first) throw Error(SP_ERR_ARG, "sp_plan_haplotypes has not been called");
     const int nh = c->plan_last - c->plan_first + 1;
     const int64_t ntiles = c->tiles_per_slot * nh;
-    materialise_kernel<<<(unsigned)ntiles, 256, 0, c->stream>>>(c->d_ref.p, c->d_payload.p, c->d_aux.p, c->d_seg_dst.p,
-                                                                c->d_seg_src.p, c->d_seg_base.p, c->d_tile_first.p,
-                                                                c->d_out.p, c->slot_stride, c->tiles_per_slot, nh);
+    launch_materialise(c->stream, ntiles, c->d_ref.p, c->d_payload.p, c->d_aux.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_seg_base.p,
+                       c->d_tile_desc.p, c->d_out.p, c->slot_stride, c->tiles_per_slot, nh);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     c->materialised = true;
@@ -380,15 +460,14 @@ void materialise(sp_ctx* c) {
 // n_slots slots of `stride` bytes; slot s owns segments [seg_base[s], seg_base[s+1]) laid out as plan_kernel does:
 // ascending seg_dst, then a PAD segment at the slot's total length and a sentinel with dst = INT64_MAX.
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, int32_t* tile_first, uint8_t* out, int64_t stride,
+                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
                        int n_slots) {
     const int64_t tiles_per_slot = stride / TILE_BYTES;
     const int64_t ntiles = tiles_per_slot * n_slots;
     if (ntiles <= 0) return;
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "tiled copy: too many tiles");
-    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, c->stream>>>(seg_dst, seg_base, n_slots, tiles_per_slot, tile_first);
-    materialise_kernel<<<(unsigned)ntiles, 256, 0, c->stream>>>(src, payload, aux, seg_dst, seg_src, seg_base, tile_first, out,
-                                                                stride, tiles_per_slot, n_slots);
+    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, c->stream>>>(seg_dst, seg_src, seg_base, n_slots, tiles_per_slot, tile_desc);
+    launch_materialise(c->stream, ntiles, src, payload, aux, seg_dst, seg_src, seg_base, tile_desc, out, stride, tiles_per_slot, n_slots);
     c->launches += 2;
     SP_CUDA(cudaGetLastError());
 }

@@ -27,7 +27,7 @@
 namespace sp {
 
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, int32_t* tile_first, uint8_t* out, int64_t stride,
+                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
                        int n_slots);
 
 struct MixSource {
@@ -43,7 +43,7 @@ struct ReadMixState {
     DevBuf<uint64_t> d_key, d_key2;
     DevBuf<int32_t> d_idx, d_idx2;
     DevBuf<int64_t> d_len, d_out_off, d_seg_dst, d_seg_src, d_seg_base;
-    DevBuf<int32_t> d_tile_first;
+    DevBuf<TileDesc> d_tile_first;
     DevBuf<uint8_t> d_aux, d_tmp, d_out;
     int64_t n_reads = 0, out_bytes = 0;
     std::vector<int64_t> h_out_off;
@@ -156,6 +156,9 @@ static void mix_finish(sp_ctx* c, int64_t shuffle_seed) {
     M.n_reads = n_kept;
     M.out_bytes = A.bytes + (M.n_sources > 1 ? B.bytes : 0);
     for (auto& e : M.ev) if (!e) SP_CUDA(cudaEventCreate(&e));
+    const int64_t stride = std::max<int64_t>(TILE_BYTES, (M.out_bytes + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES);
+    M.d_tile_first.reserve((size_t)(stride / TILE_BYTES));
+    M.d_out.reserve((size_t)stride, 0.02);
     SP_CUDA(cudaEventRecord(M.ev[0], st));
     const size_t n1s = (size_t)std::max<int64_t>(n, 1);
     M.d_key.reserve(n1s); M.d_key2.reserve(n1s); M.d_idx.reserve(n1s); M.d_idx2.reserve(n1s);
@@ -188,9 +191,6 @@ static void mix_finish(sp_ctx* c, int64_t shuffle_seed) {
     c->launches += 4 + 3;  // four kernels of this file + cub's scans and sort (counted as one each)
     SP_CUDA(cudaGetLastError());
     SP_CUDA(cudaEventRecord(M.ev[1], st));
-    const int64_t stride = std::max<int64_t>(TILE_BYTES, (M.out_bytes + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES);
-    M.d_tile_first.reserve((size_t)(stride / TILE_BYTES));
-    M.d_out.reserve((size_t)stride, 0.02);
     launch_tiled_copy(c, A.records.p, B.records.p, M.d_aux.p, M.d_seg_dst.p, M.d_seg_src.p, M.d_seg_base.p, M.d_tile_first.p,
                       M.d_out.p, stride, 1);
     SP_CUDA(cudaEventRecord(M.ev[2], st));
