@@ -496,9 +496,18 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
         SP_CUDA(cudaMemcpyAsync(R.d_order.p, R.h_order.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
     }
     int ctas_per_sm = 1;
+    {   // the generator state columns are 17 KB per CTA: ask for the largest shared-memory carve-out, or the default split
+        // (about 100 KB) holds five CTAs per SM where the register file holds eight
+        static bool carveout_set = false;
+        if (!carveout_set) {
+            SP_CUDA(cudaFuncSetAttribute(reads_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            carveout_set = true;
+        }
+    }
     if (replay) SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<true>, RD_THREADS, 0));
     else SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<false>, RD_THREADS, 0));
     ctas_per_sm = std::max(1, ctas_per_sm);
+    if (const char* e = getenv("SYNTHPOP_READS_CTAS_PER_SM")) ctas_per_sm = std::max(1, std::min(ctas_per_sm, atoi(e)));  // tuning hook
     const int64_t want_ctas = (n_reads + RD_THREADS - 1) / RD_THREADS;
     const int64_t grid_full = std::min<int64_t>(want_ctas, (int64_t)c->sm_count * ctas_per_sm);
     const int64_t words = ((int64_t)max_len + 3) / 4 + 1;
