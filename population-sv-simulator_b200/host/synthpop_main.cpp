@@ -28,7 +28,7 @@ int main(int argc, char** argv) {
         else break;
     }
     if (a >= argc) {
-        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|pbsim> <argv of the reference's command>\n");
+        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|pbsim|haplotype2reads> <argv of the reference's command>\n");
         return 2;
     }
     const std::string cls = argv[a++];
@@ -117,6 +117,25 @@ int main(int argc, char** argv) {
             sp_destroy(ctx);
             return 255;
         }
+    } else if (cls == "haplotype2reads") {
+        // docker/haplotype2reads.sh:16-24,31-32,53-64 for one individual, without the haplotype_<i>.fa files and the bucket:
+        // ID1 LENGTH_MIN LENGTH_MAX LENGTH_MEAN LENGTH_STDEV MAX_COVERAGE REFERENCE_FILE HAPLOTYPE2VARIANTS_FILE VARIANTS_FILE
+        // HMM_MODEL OUTPUT_FILE   (ID2 = ID1 + 1; the pbsim options are the script's PBSIM2_COMMAND)
+        if (args.size() < 11) { fprintf(stderr, "usage: haplotype2reads ID1 LENGTH_MIN LENGTH_MAX LENGTH_MEAN LENGTH_STDEV MAX_COVERAGE REFERENCE_FILE HAPLOTYPE2VARIANTS_FILE VARIANTS_FILE HMM_MODEL OUTPUT_FILE\n"); return 2; }
+        sp_read_args ra;
+        memset(&ra, 0, sizeof ra);
+        ra.length_min = atoll(args[1]); ra.length_max = atoll(args[2]); ra.length_mean = atof(args[3]); ra.length_sd = atof(args[4]);
+        ra.depth = atof(args[5]);
+        ra.accuracy_min = 0.99; ra.accuracy_max = 1.0; ra.accuracy_mean = 0.995;
+        ra.sub_ratio = 6; ra.ins_ratio = 50; ra.del_ratio = 54;
+        ra.hmm_model = args[9];
+        ra.seed = (uint32_t)seed;
+        rc = sp_load_reference_fasta(ctx, args[6]);
+        if (rc == SP_OK) rc = sp_load_population(ctx, args[7], args[8]);
+        if (rc == SP_OK) rc = sp_reads_configure(ctx, &ra);
+        int64_t n_reads = 0, n_bytes = 0;
+        if (rc == SP_OK) rc = sp_haplotype2reads(ctx, atoi(args[0]), seed, args[10], &n_reads, &n_bytes);
+        if (rc == SP_OK) fprintf(stderr, "%lld reads, %lld bytes\n", (long long)n_reads, (long long)n_bytes);
     } else {
         fprintf(stderr, "synthpop: unknown class %s\n", cls.c_str());
         sp_destroy(ctx);
