@@ -81,6 +81,20 @@ struct DrawStream {
         for (int j = 0; j < 31; j++) st[j * RD_THREADS] = r[j];
         f = 3; used = 0;
     }
+    // rand() at a ring position the caller knows at compile time (after unrolling): no index arithmetic, f and used are
+    // brought up to date by skip() once the unrolled block is over
+    __device__ __forceinline__ uint32_t next_at(int fi) {
+        if (REPLAY) return (uint32_t)__ldg(replay + used++);
+        const int b = fi >= 3 ? fi - 3 : fi + 28;
+        const uint32_t v = st[fi * RD_THREADS] + st[b * RD_THREADS];
+        st[fi * RD_THREADS] = v;
+        return v >> 1;
+    }
+    __device__ __forceinline__ void skip(uint32_t n) {  // account for n draws made through next_at
+        if (REPLAY) return;
+        used += n;
+        f = (int)((uint32_t)(f + n) % 31u);
+    }
     __device__ __forceinline__ uint32_t next() {
         if (REPLAY) return (uint32_t)__ldg(replay + used++);
         const int b = f >= 3 ? f - 3 : f + 28;
@@ -123,19 +137,26 @@ __device__ __forceinline__ void job_error(const ReadJob& J, int code, int64_t r)
 // The oriented, upper-cased template (:2316-2341): seq[t] for t in [0, len'), fetched through aligned 8-byte chunks.
 // The strand is data (a step of +-1 and an xor mask), not a branch: the threads of a warp alternate strands.
 struct Template {
-    const uint8_t* origin;  // address of seq[0]: first base of the window (+) or its last base (-)
-    int32_t dir;            // +1 / -1
-    uint32_t rev;           // 0 / 0xff
-    int64_t cur;            // index of the cached chunk on the 8-byte grid of the address space
-    uint64_t chunk;
+    const unsigned long long* base8;  // 8-byte aligned address at or below seq[0]
+    int32_t o0;                       // seq[0] - base8, 0..7
+    int32_t dir;                      // +1 / -1
+    uint32_t rev;                     // 0 / 0xff
+    int32_t cur;                      // index (relative to base8) of the cached 8-byte chunk
+    uint32_t lo, hi;
     __device__ __forceinline__ void begin(const uint8_t* w, int32_t lp, bool forward) {
-        origin = forward ? w : w + (lp - 1); dir = forward ? 1 : -1; rev = forward ? 0u : 0xffu; cur = -1; chunk = 0;
+        const uint8_t* origin = forward ? w : w + (lp - 1);  // first base of the window (+) or its last base (-)
+        o0 = (int32_t)((uintptr_t)origin & 7);
+        base8 = (const unsigned long long*)(origin - o0);
+        dir = forward ? 1 : -1; rev = forward ? 0u : 0xffu; cur = INT32_MIN; lo = hi = 0;
     }
     __device__ __forceinline__ uint8_t at(int32_t t) {
-        const uintptr_t a = (uintptr_t)(origin + (int64_t)dir * t);
-        const int64_t id = (int64_t)(a >> 3);
-        if (id != cur) { chunk = __ldg((const unsigned long long*)(a & ~(uintptr_t)7)); cur = id; }
-        uint32_t c = (uint32_t)(chunk >> (8 * (a & 7))) & 0xffu;
+        const int32_t rel = o0 + dir * t;   // 32-bit: a read is far shorter than 2^31 bases
+        const int32_t w = rel >> 3;         // floor, also for the negative offsets of the reverse strand
+        if (w != cur) {
+            const unsigned long long chunk = __ldg(base8 + w);
+            lo = (uint32_t)chunk; hi = (uint32_t)(chunk >> 32); cur = w;
+        }
+        uint32_t c = __byte_perm(lo, hi, (uint32_t)(rel & 7)) & 0xffu;
         c -= (c - 'a' <= 'z' - 'a') ? 32u : 0u;  // toupper
         // complement: A(0x41)<->T(0x54) differ by 0x15, C(0x43)<->G(0x47) by 0x04; anything else stays
         const uint32_t x = (c == 'A' || c == 'T') ? 0x15u : (c == 'C' || c == 'G') ? 0x04u : 0u;
@@ -205,27 +226,46 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     __syncwarp(mask);
 
     // ---- quality codes (:1657-1680), four per scratch word; the deletion counters are cleared on the way
+    // Every read reaches this point after the same number of draws, so the ring position of each quality draw is a
+    // function of the base index alone: blocks of 31 bases are unrolled with compile-time ring positions.
     if (T.exist_hmm[acc]) {
         const int a51 = acc * 51;
-        uint32_t st = __ldg(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);
+        uint32_t st = __ldg(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);  // third draw: f is 6 now
         uint32_t word = 0;
+        if (len > 0) word = hmm_emis(T, a51, st, S.next_at(6));
+        // base p >= 1 draws at ring positions 5+2p (transition) and 6+2p (emission), mod 31
 #pragma unroll 1
-        for (int32_t p = 0; p < len; p++) {
-            if (p > 0) st = hmm_tran(T, a51, st, S.next());
-            word |= hmm_emis(T, a51, st, S.next()) << (8 * (p & 3));
-            if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+        for (int32_t p0 = 1; p0 < len; p0 += 31) {
+#pragma unroll
+            for (int j = 0; j < 31; j++) {
+                const int32_t p = p0 + j;
+                if (p < len) {
+                    st = hmm_tran(T, a51, st, S.next_at((7 + 2 * j) % 31));
+                    word |= hmm_emis(T, a51, st, S.next_at((8 + 2 * j) % 31)) << (8 * (p & 3));
+                    if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+                }
+            }
         }
         if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; }
+        if (len > 0) S.skip(2u * (uint32_t)len - 1u);
     } else {
         const uint4 mf = __ldg((const uint4*)(T.mod_freq + acc));
         const uint8_t* f2q = T.freq2qc + acc * 1001;
         uint32_t word = 0;
+        // two draws so far (f is 5): base p draws at ring position 5+p mod 31
 #pragma unroll 1
-        for (int32_t p = 0; p < len; p++) {
-            word |= (uint32_t)__ldg(f2q + fastmod(S.next(), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
-            if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+        for (int32_t p0 = 0; p0 < len; p0 += 31) {
+#pragma unroll
+            for (int j = 0; j < 31; j++) {
+                const int32_t p = p0 + j;
+                if (p < len) {
+                    word |= (uint32_t)__ldg(f2q + fastmod(S.next_at((5 + j) % 31), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
+                    if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+                }
+            }
         }
         if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; }
+        S.skip((uint32_t)len);
     }
     __syncwarp(mask);
 
