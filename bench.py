@@ -257,7 +257,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--batch", type=int, default=125, help="haplotypes per step (per GPU)")
     ap.add_argument("--length", type=int, default=CHR1)
-    ap.add_argument("--e2e-haplotypes", type=int, default=8)
+    ap.add_argument("--e2e-haplotypes", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="genotype/collision kernels on the materialisation stream")
     ap.add_argument("--read-haplotypes", type=int, default=2, help="haplotypes of the CCS read leg (0 = skip)")
