@@ -226,6 +226,8 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     __syncwarp(mask);
 
     // ---- quality codes (:1657-1680), four per scratch word; the deletion counters are cleared on the way
+    uint32_t qmin4 = 0xffffffffu;  // bytewise minimum of the quality words: the read's lowest quality code bounds every
+                                   // acceptance threshold of the deletion loop below
     // Every read reaches this point after the same number of draws, so the ring position of each quality draw is a
     // function of the base index alone: blocks of 31 bases are unrolled with compile-time ring positions.
     if (T.exist_hmm[acc]) {
@@ -242,11 +244,11 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
                 if (p < len) {
                     st = hmm_tran(T, a51, st, S.next_at((7 + 2 * j) % 31));
                     word |= hmm_emis(T, a51, st, S.next_at((8 + 2 * j) % 31)) << (8 * (p & 3));
-                    if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+                    if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; qmin4 = __vminu4(qmin4, word); word = 0; }
                 }
             }
         }
-        if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; }
+        if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; qmin4 = __vminu4(qmin4, word | (0xffffffffu << (8 * (len & 3)))); }
         if (len > 0) S.skip(2u * (uint32_t)len - 1u);
     } else {
         const uint4 mf = __ldg((const uint4*)(T.mod_freq + acc));
@@ -260,11 +262,11 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
                 const int32_t p = p0 + j;
                 if (p < len) {
                     word |= (uint32_t)__ldg(f2q + fastmod(S.next_at((5 + j) % 31), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
-                    if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; word = 0; }
+                    if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; qmin4 = __vminu4(qmin4, word); word = 0; }
                 }
             }
         }
-        if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; }
+        if (len & 3) { qw[(len >> 2) * 32] = word; dw[(len >> 2) * 32] = 0; qmin4 = __vminu4(qmin4, word | (0xffffffffu << (8 * (len & 3)))); }
         S.skip((uint32_t)len);
     }
     __syncwarp(mask);
@@ -272,6 +274,8 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     // ---- deletions by rejection (:2282-2292). The loop is driven by a warp vote so that the threads stay in step.
     {
         const FastMod ml = make_fastmod_dev((uint32_t)max(len - 1, 1));
+        const uint32_t qm = min(min(qmin4 & 255u, (qmin4 >> 8) & 255u), min((qmin4 >> 16) & 255u, qmin4 >> 24));
+        const int32_t tmax = s_thre[3 * PB_NQ + min(qm, (uint32_t)(PB_NQ - 1))];
         int32_t num = 0;
 #pragma unroll 1
         for (;;) {
@@ -280,6 +284,9 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
             if (more) {
                 const uint32_t pos = fastmod(S.next(), ml.M, ml.sh, ml.d);
                 const int32_t v = (int32_t)(S.next() % 1000000u);
+                // v >= the largest threshold any position of this read can have: rejected whatever q[pos] is, and the
+                // scattered read of q[pos] (one HBM access for one byte) is not made. Same decision, same draws.
+                if (v >= tmax) continue;
                 const uint32_t sh = 8 * (pos & 3);
                 const int qv = (qw[(pos >> 2) * 32] >> sh) & 255u;
                 if (v < s_thre[qv]) {
@@ -373,9 +380,14 @@ template <bool REPLAY>
 __global__ void __launch_bounds__(RD_THREADS)
 reads_kernel(const ReadJob J, const ReadTablesDev T) {
     __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
-    __shared__ int32_t s_thre[3 * PB_NQ];
+    __shared__ int32_t s_thre[4 * PB_NQ];  // err_thre, sub_thre, ins_thre, then max(err_thre[q..93])
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 3 * PB_NQ; i += blockDim.x) s_thre[i] = T.thre[i];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int32_t m = 0;
+        for (int q = PB_NQ - 1; q >= 0; q--) { m = max(m, s_thre[q]); s_thre[3 * PB_NQ + q] = m; }
+    }
     __syncthreads();
     const int64_t gw = (int64_t)blockIdx.x * (RD_THREADS / 32) + w;
     uint32_t* qw = J.scratch + gw * 2 * J.scratch_words * 32 + lane;

@@ -17,7 +17,7 @@ synth.write_hmm_model(model, quality=os.environ.get("PROFILE_QUALITY", "phred"))
 bases, _, _ = synth.random_reference(L, 7)
 with sp.Context(0, 42) as ctx:
     opts = ["--length-min", "5000", "--length-max", "30000", "--accuracy-min", "0.99", "--accuracy-max", "1.0",
-            "--difference-ratio", "6:50:54", "--length-mean", "15000", "--length-sd", "2000", "--accuracy-mean", "0.995",
+            "--difference-ratio", os.environ.get("PROFILE_RATIO", "6:50:54"), "--length-mean", "15000", "--length-sd", "2000", "--accuracy-mean", "0.995",
             "--depth", str(depth), "--hmm_model", model, "--seed", "42"]
     args, _ = sp.ReadArgs.from_options(opts, stream_mode=sp.READS_PER_READ_STREAMS)
     ctx.reads_configure(args)
