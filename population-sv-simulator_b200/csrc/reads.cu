@@ -548,11 +548,13 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
         SP_CUDA(cudaMemcpyAsync(R.d_order.p, R.h_order.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
     }
     int ctas_per_sm = 1;
-    {   // the generator state columns are 17 KB per CTA: ask for the largest shared-memory carve-out, or the default split
-        // (about 100 KB) holds five CTAs per SM where the register file holds eight
+    {   // Shared memory against L1: the generator state columns are 17 KB per CTA, but the table walks, the template
+        // chunks and the scratch words live in L1. Measured at 30x chr1: the driver's default split (5 CTAs per SM, large
+        // L1) 88 ms, the largest carve-out (8 CTAs per SM) 119 ms. SYNTHPOP_READS_CARVEOUT (percent) is a tuning hook.
         static bool carveout_set = false;
         if (!carveout_set) {
-            SP_CUDA(cudaFuncSetAttribute(reads_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            if (const char* e = getenv("SYNTHPOP_READS_CARVEOUT"))
+                SP_CUDA(cudaFuncSetAttribute(reads_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
             carveout_set = true;
         }
     }
