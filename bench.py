@@ -96,14 +96,21 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
     ctx.plan_haplotypes(first_hap, first_hap + n_haps - 1, False)
     ctx.materialise()
     ctx.synchronize()
-    l0 = ctx.kernel_launches
-    # warm-up on the first haplotype (allocations, table upload), then the timed pass over all of them
+    # warm-up (allocations, table upload): one whole individual when the reads are mixed, so that the three buffer sets the
+    # mix rotates (two sources + the simulator's own) exist before the timed pass, as they do from the second individual on
+    mix = n_haps == 2   # an individual: the two haplotypes' reads are shuffled into one file on the device
+    if mix:
+        ctx.reads_mix_begin()
+        for h in range(first_hap, first_hap + n_haps):
+            ctx.reads_simulate_haplotype(h, 1)
+            ctx.reads_mix_add()
+        ctx.reads_mix_finish(41)
     ctx.reads_simulate_haplotype(first_hap, 1)
     torch.cuda.synchronize()
+    l0 = ctx.kernel_launches
     t0 = time.perf_counter()
     bases = reads = dropped = 0
     k_ms = p_ms = 0.0
-    mix = n_haps == 2   # an individual: the two haplotypes' reads are shuffled into one file on the device
     used = None
     if mix:
         ctx.reads_mix_begin()

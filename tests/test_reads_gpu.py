@@ -180,3 +180,44 @@ def test_pbsim_argument_errors(sp, tmp_path):
         ctx.reads_configure(args)
         with pytest.raises(sp.SynthpopError, match="too short"):
             ctx.reads_simulate_sequence(np.frombuffer(b"ACGT" * 10, np.uint8))
+
+
+def test_full_size_30x_chr1_properties(sp, tmp_path):
+    """BASELINE configs[3] at full size (30x CCS over one chr1-sized haplotype, ~7.5 Gbp of reads): too large for the
+    CPU restatement, so the size-independent properties of simulate_by_model are checked instead — the quota rule
+    (docker/pbsim2.cpp:1641-1650), the record layout (:1710-1711), the NNNNN filter (:1709), determinism, and independence of the
+    per-read streams from what else ran on the context."""
+    from synthpop import synth
+    L = 248_956_422
+    hap, _, _ = synth.random_reference(L, 11)
+    model = str(tmp_path / "hmm.model"); synth.write_hmm_model(model, quality="phred")
+    p = dict(CCS, depth=30.0)
+    with sp.Context(0, 42) as ctx:
+        _configure(sp, ctx, p, 42, model, False, sp.READS_PER_READ_STREAMS)
+        res = ctx.reads_simulate_sequence(hap)
+        quota = int(30.0 * L)
+        assert quota <= res["bases"] < quota + p["len_min"]            # the last read is clipped to the quota or to len_min
+        ln, dr, used = ctx.reads_log(res["n_reads"])
+        assert int(ln.sum()) == res["bases"] and int(dr.sum()) == res["n_dropped"] > 0
+        assert ln.min() >= 2 and ln[:-1].min() >= p["len_min"] and ln.max() <= p["len_max"]
+        assert int(used.astype(np.int64).sum()) >= 3 * res["bases"]    # 2 quality draws + 1 error draw per base at least
+        buf = ctx.reads_copy(res["file_bytes"])
+        kept = res["n_reads"] - res["n_dropped"]
+        assert int(np.count_nonzero(buf == ord("\n"))) == kept and int(np.count_nonzero(buf == ord("Z"))) == kept
+        assert int(np.count_nonzero(buf == ord(">"))) == kept and buf[0] == ord(">") and buf[-1] == ord("\n")
+        hist = np.bincount(buf, minlength=256)
+        allowed = np.zeros(256, bool); allowed[list(b"ACGTN>SZ_\n0123456789")] = True
+        assert hist[~allowed].sum() == 0
+        # sequence bytes = file bytes minus the names: the bases of the kept reads
+        seq_bytes = int(hist[list(b"ACGTN")].sum())
+        assert seq_bytes == int(ln[dr == 0].sum())
+        # no kept record contains NNNNN (bytes.find scans at memory speed)
+        assert buf.tobytes().find(b"NNNNN") == -1
+        checksum = int(np.add.reduce(buf[::7].astype(np.uint64) * np.arange(buf[::7].size, dtype=np.uint64) % np.uint64(1000003)))
+        # determinism, and independence from the context's history: another sequence in between, then the same again
+        ctx.reads_simulate_sequence(hap[: 3_000_000])
+        res2 = ctx.reads_simulate_sequence(hap)
+        assert res2 == res
+        buf2 = ctx.reads_copy(res2["file_bytes"])
+        assert int(np.add.reduce(buf2[::7].astype(np.uint64) * np.arange(buf2[::7].size, dtype=np.uint64) % np.uint64(1000003))) == checksum
+        assert np.array_equal(buf2[:50_000_000], buf[:50_000_000]) and np.array_equal(buf2[-50_000_000:], buf[-50_000_000:])
