@@ -140,7 +140,7 @@ static void mix_add(sp_ctx* c) {
     S.n_reads = R.n_reads; S.n_kept = R.n_reads - R.n_dropped; S.bytes = R.out_bytes;
     S.id_len = (int32_t)(1 + R.par.id_prefix.size() + std::to_string(R.ref_num).size() + 1);
     R.n_reads = 0; R.n_dropped = 0; R.out_bytes = 0; R.emitted_bases = 0; R.results_on_host = false;
-    R.h_len.clear(); R.h_rec_off.assign(1, 0);
+    R.h_len.clear(); R.h_rec_off.assign(1, 0); R.plan_on_device = false;
     M.mixed = false;
 }
 

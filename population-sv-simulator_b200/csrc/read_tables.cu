@@ -334,6 +334,7 @@ void reads_configure(sp_ctx* c, const sp_read_args* a) {
     R.have_replay = false;
     R.n_reads = 0;
     R.configured = true;
+    R.plan_tables_stale = true;
 }
 
 void free_reads(sp_ctx* c) {

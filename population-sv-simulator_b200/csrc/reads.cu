@@ -18,6 +18,8 @@
 // Everything is integer arithmetic; the only floating-point expressions of the reference's loop (:1682, :2282) are
 // evaluated on the host with the reference's own types when the per-read plan is made.
 #include "reads.h"
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include <chrono>
 
@@ -444,6 +446,157 @@ static int count_digits(long long v) {
     return n;
 }
 
+// ---- the per-read plan on the device (per-read-stream mode) ---------------------------------------------------------
+// simulate_by_model's loop header (:1641-1655) decides, from the first two draws of every read, its length and accuracy
+// class; the loop ends with the read that reaches the quota. With one stream per read the draws of read i do not depend
+// on the reads before it, so the header is a map + an inclusive scan + a cut, not a sequential loop.
+__global__ void __launch_bounds__(128)
+plan_lengths_kernel(uint32_t seed, int64_t ref_num, int64_t n, const int32_t* __restrict__ prob2len,
+                    const uint8_t* __restrict__ prob2acc, uint32_t len_rv, uint32_t acc_rv, int64_t* __restrict__ len64,
+                    uint8_t* __restrict__ acc) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t r[31];
+    glibc_seed(read_seed(seed, ref_num, i), r);
+    r[3] += r[0];
+    const uint32_t d0 = r[3] >> 1, d1 = (r[4] + r[1]) >> 1;
+    len64[i] = prob2len[d0 % len_rv + 1];       // :1642
+    acc[i] = prob2acc[d1 % acc_rv + 1];         // :1654-1655
+}
+
+// res[0] = number of reads (the first read whose inclusive length sum reaches the quota is the last, :1641), res[1] =
+// bases emitted; the last read is clipped to the quota, but not below len_min (:1643-1650).
+__global__ void __launch_bounds__(256)
+plan_cut_kernel(int64_t n, const int64_t* __restrict__ scan, int64_t* __restrict__ len64, int64_t quota, int64_t len_min,
+                int64_t* __restrict__ res) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t prev = i ? scan[i - 1] : 0;
+    if (prev < quota && scan[i] >= quota) {
+        int64_t len = len64[i];
+        if (prev + len > quota) {
+            len = quota - prev;
+            if (len < len_min) len = len_min;
+        }
+        len64[i] = len;
+        res[0] = i + 1;
+        res[1] = prev + len;
+    }
+}
+
+// Per read: del_num_total = int((float)len * del_thre / 1000000 + 0.5) (:2282; the reference's own types: a float product
+// and quotient, then a double sum), the record length of ">" id n "Z" seq "\n", the longest read.
+__global__ void __launch_bounds__(256)
+plan_finish_kernel(int64_t n_reads, const int64_t* __restrict__ len64, const uint8_t* __restrict__ acc,
+                   const int32_t* __restrict__ delthre, int32_t no_error, int32_t id_len, int32_t* __restrict__ len,
+                   int32_t* __restrict__ ndel, int64_t* __restrict__ reclen, int64_t* __restrict__ res) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n_reads) return;
+    if (i == n_reads) { reclen[i] = 0; return; }
+    const int32_t l = (int32_t)len64[i];
+    const float q = __fdiv_rn(__fmul_rn((float)(long long)l, (float)(long long)delthre[acc[i]]), 1000000.0f);
+    const int32_t nd = (int32_t)((double)q + 0.5);
+    len[i] = l; ndel[i] = nd;
+    int digits = 1;
+    for (int64_t v = i + 1; v >= 10; v /= 10) digits++;
+    reclen[i] = (int64_t)id_len + digits + 1 + (no_error ? (int64_t)l + nd : (int64_t)l) + 1;
+    atomicMax((unsigned long long*)&res[2], (unsigned long long)l);
+}
+
+// Grouping key of the read kernel's work order: longest first, then by accuracy class (stable in the read index).
+__global__ void __launch_bounds__(256)
+plan_keys_kernel(int64_t n_reads, const int32_t* __restrict__ len, const uint8_t* __restrict__ acc,
+                 const int64_t* __restrict__ res, int32_t* __restrict__ key, int32_t* __restrict__ idx) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    const int32_t max_len = max((int32_t)res[2], 2);
+    const int32_t width = max(1, (max_len + 63) / 64);
+    key[i] = (63 - min(63, len[i] / width)) * 101 + (int32_t)acc[i];
+    idx[i] = (int32_t)i;
+}
+
+// Fills d_len, d_ndel, d_acc, d_rec_off, d_order for one sequence; returns the number of reads.
+static int64_t plan_reads_on_device(sp_ctx* c, ReadState& R, int64_t ref_num, long long quota, int32_t id_len,
+                                    int32_t* max_len_out, int64_t* bases_out, int64_t* bytes_out) {
+    const ReadParams& p = R.par;
+    const ReadTablesHost& t = R.tab;
+    cudaStream_t st = c->stream;
+    if (R.plan_tables_stale) {
+        R.d_prob2len.reserve(t.prob2len.size()); R.d_prob2acc.reserve(t.prob2accuracy.size()); R.d_delthre.reserve(PB_ACCURACY_MAX + 1);
+        int32_t delthre[PB_ACCURACY_MAX + 1];
+        for (int a = 0; a <= PB_ACCURACY_MAX; a++) delthre[a] = (int32_t)(long)int(((100 - a) * p.del_rate) * 10000 + 0.5);  // :1682
+        SP_CUDA(cudaMemcpyAsync(R.d_prob2len.p, t.prob2len.data(), t.prob2len.size() * 4, cudaMemcpyHostToDevice, st));
+        SP_CUDA(cudaMemcpyAsync(R.d_prob2acc.p, t.prob2accuracy.data(), t.prob2accuracy.size(), cudaMemcpyHostToDevice, st));
+        SP_CUDA(cudaMemcpyAsync(R.d_delthre.p, delthre, sizeof delthre, cudaMemcpyHostToDevice, st));
+        SP_CUDA(cudaStreamSynchronize(st));
+        R.plan_tables_stale = false;
+    }
+    R.d_planres.reserve(4);
+    int64_t res[4] = {-1, 0, 0, 0};
+    if (quota <= 0) { *max_len_out = 2; *bases_out = 0; *bytes_out = 0; return 0; }
+    const double mean_len = std::max(1.0, std::min(p.len_mean, (double)p.len_max));
+    int64_t n = (int64_t)((double)quota / mean_len * 1.05) + 1024;
+    for (;;) {
+        n = std::min<int64_t>(n, (int64_t)1 << 27);
+        R.d_len64.reserve((size_t)n); R.d_scan.reserve((size_t)n); R.d_acc.reserve((size_t)n);
+        size_t tmp = 0;
+        cub::DeviceScan::InclusiveSum(nullptr, tmp, R.d_len64.p, R.d_scan.p, (int)n, st);
+        R.d_cubtmp.reserve(tmp + 256);
+        SP_CUDA(cudaMemcpyAsync(R.d_planres.p, res, sizeof res, cudaMemcpyHostToDevice, st));
+        plan_lengths_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(p.seed, ref_num, n, R.d_prob2len.p, R.d_prob2acc.p,
+                                                                         (uint32_t)t.len_rand_value, (uint32_t)t.accuracy_rand_value,
+                                                                         R.d_len64.p, R.d_acc.p);
+        tmp = R.d_cubtmp.cap;
+        SP_CUDA(cub::DeviceScan::InclusiveSum(R.d_cubtmp.p, tmp, R.d_len64.p, R.d_scan.p, (int)n, st));
+        plan_cut_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, R.d_scan.p, R.d_len64.p, quota, p.len_min, R.d_planres.p);
+        c->launches += 3;
+        SP_CUDA(cudaGetLastError());
+        SP_CUDA(cudaMemcpyAsync(res, R.d_planres.p, sizeof res, cudaMemcpyDeviceToHost, st));
+        SP_CUDA(cudaStreamSynchronize(st));
+        if (res[0] >= 0) break;
+        if (n >= ((int64_t)1 << 27)) throw Error(SP_ERR_ARG, "read plan: more than 2^27 reads in one sequence");
+        res[0] = -1; res[1] = 0; res[2] = 0; res[3] = 0;
+        n *= 2;
+    }
+    const int64_t n_reads = res[0];
+    const size_t n1 = (size_t)std::max<int64_t>(n_reads, 1);
+    R.d_len.reserve(n1); R.d_ndel.reserve(n1); R.d_reclen.reserve(n1 + 1); R.d_rec_off.reserve(n1 + 1);
+    R.d_key.reserve(n1); R.d_key2.reserve(n1); R.d_idx.reserve(n1); R.d_order.reserve(n1);
+    size_t tmp_scan = 0, tmp_sort = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_scan, R.d_reclen.p, R.d_rec_off.p, (int)(n_reads + 1), st);
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, R.d_key.p, R.d_key2.p, R.d_idx.p, R.d_order.p, (int)n_reads, 0, 13, st);
+    R.d_cubtmp.reserve(std::max(tmp_scan, tmp_sort) + 256);
+    const unsigned g = (unsigned)((n_reads + 256) / 256);
+    plan_finish_kernel<<<g, 256, 0, st>>>(n_reads, R.d_len64.p, R.d_acc.p, R.d_delthre.p, p.no_error ? 1 : 0, id_len, R.d_len.p,
+                                          R.d_ndel.p, R.d_reclen.p, R.d_planres.p);
+    size_t tmp = R.d_cubtmp.cap;
+    SP_CUDA(cub::DeviceScan::ExclusiveSum(R.d_cubtmp.p, tmp, R.d_reclen.p, R.d_rec_off.p, (int)(n_reads + 1), st));
+    plan_keys_kernel<<<g, 256, 0, st>>>(n_reads, R.d_len.p, R.d_acc.p, R.d_planres.p, R.d_key.p, R.d_idx.p);
+    tmp = R.d_cubtmp.cap;
+    SP_CUDA(cub::DeviceRadixSort::SortPairs(R.d_cubtmp.p, tmp, R.d_key.p, R.d_key2.p, R.d_idx.p, R.d_order.p, (int)n_reads, 0, 13, st));
+    c->launches += 4;
+    SP_CUDA(cudaGetLastError());
+    int64_t total = 0;
+    SP_CUDA(cudaMemcpyAsync(res, R.d_planres.p, sizeof res, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(&total, R.d_rec_off.p + n_reads, 8, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaStreamSynchronize(st));
+    *max_len_out = std::max<int32_t>(2, (int32_t)res[2]);
+    *bases_out = res[1];
+    *bytes_out = total;
+    return n_reads;
+}
+
+// h_len / h_rec_off of the current batch, fetched only when a caller asks for the per-read log or the file bytes
+static void ensure_host_plan(sp_ctx* c, ReadState& R) {
+    if (!R.plan_on_device) return;
+    R.h_len.assign((size_t)R.n_reads, 0);
+    R.h_rec_off.assign((size_t)R.n_reads + 1, 0);
+    if (R.n_reads > 0) SP_CUDA(cudaMemcpyAsync(R.h_len.data(), R.d_len.p, (size_t)R.n_reads * 4, cudaMemcpyDeviceToHost, c->stream));
+    SP_CUDA(cudaMemcpyAsync(R.h_rec_off.data(), R.d_rec_off.p, ((size_t)R.n_reads + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+    SP_CUDA(cudaStreamSynchronize(c->stream));
+    R.plan_on_device = false;
+}
+
 // simulate_by_model's loop header and per-read plan (:1641-1655, :1682, :2282) for every read of one sequence, then the
 // read kernel. d_seq must stay valid until the stream has run the kernel.
 static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64_t ref_num) {
@@ -459,93 +612,111 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     if (replay && !R.have_replay) throw Error(SP_ERR_ARG, "replay mode: sp_reads_set_replay has not been called");
     R.h_len.clear(); R.h_acc.clear(); R.h_ndel.clear();
     R.results_on_host = false;
-    long long len_total = 0;
-    std::vector<int32_t> first;  // two draws per read of the current batch
-    int64_t batch0 = 0, batch_n = 0;
-    auto fetch_batch = [&](int64_t r0) {
-        if (replay) {
-            batch0 = 0; batch_n = (int64_t)R.replay_off.size();
-            first.resize((size_t)batch_n * 2);
-            for (int64_t r = 0; r < batch_n; r++) {
-                const int64_t o = R.replay_off[r];
-                if (o < 0 || o + 1 >= (int64_t)R.replay_draws.size()) throw Error(SP_ERR_ARG, "replay: read offset outside the draw log");
-                first[2 * r] = R.replay_draws[o]; first[2 * r + 1] = R.replay_draws[o + 1];
-            }
-            return;
-        }
-        const double mean_len = std::max(1.0, std::min(p.len_mean, (double)p.len_max));
-        int64_t n = (int64_t)((double)(quota - len_total) / mean_len * 1.05) + 1024;
-        n = std::min<int64_t>(n, 1 << 26);
-        R.d_first.reserve((size_t)n * 2);
-        first_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(p.seed, ref_num, r0, n, R.d_first.p);
-        c->launches++;
-        SP_CUDA(cudaGetLastError());
-        first.resize((size_t)n * 2);
-        SP_CUDA(cudaMemcpyAsync(first.data(), R.d_first.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
-        SP_CUDA(cudaStreamSynchronize(st));
-        batch0 = r0; batch_n = n;
-    };
-    int64_t r = 0;
-    while (len_total < quota) {  // :1641
-        if (r >= batch0 + batch_n) {
-            if (replay && batch_n > 0) throw Error(SP_ERR_ARG, "replay: the log has fewer reads than the quota needs");
-            fetch_batch(r);
-            if (batch_n == 0) throw Error(SP_ERR_ARG, "replay: empty log");
-        }
-        const long d0 = first[2 * (r - batch0)], d1 = first[2 * (r - batch0) + 1];
-        long len = t.prob2len[d0 % t.len_rand_value + 1];
-        if (len_total + len > quota) {
-            len = quota - len_total;
-            if (len < p.len_min) len = p.len_min;
-        }
-        const int accuracy = t.prob2accuracy[d1 % t.accuracy_rand_value + 1];
-        const long del_thre = int(((100 - accuracy) * p.del_rate) * 10000 + 0.5);      // :1682
-        const long del_num_total = int((float)len * del_thre / 1000000 + 0.5);         // :2282 (float32 product)
-        R.h_len.push_back((int32_t)len); R.h_acc.push_back((uint8_t)accuracy); R.h_ndel.push_back((int32_t)del_num_total);
-        len_total += len;  // strlen(mut.new_seq) == len whenever len' < ref.len (the kernel rejects the other case)
-        r++;
-    }
-    if (replay && r != (int64_t)R.replay_off.size())
-        throw Error(SP_ERR_ARG, "replay: the log has " + std::to_string(R.replay_off.size()) + " reads, the quota ends after " + std::to_string(r));
-    const int64_t n_reads = r;
-    R.n_reads = n_reads; R.ref_num = (long)ref_num; R.emitted_bases = len_total;
-    // record offsets: ">" id_prefix ref_num "_" n "Z" seq "\n"
-    const std::string id = ">" + p.id_prefix + std::to_string(ref_num) + "_";
-    R.h_rec_off.assign((size_t)n_reads + 1, 0);
+    const std::string id = ">" + p.id_prefix + std::to_string(ref_num) + "_";  // record: id n "Z" seq "\n"
+    int64_t n_reads = 0;
     int32_t max_len = 2;
-    for (int64_t i = 0; i < n_reads; i++) {
-        const int64_t seqlen = p.no_error ? (int64_t)R.h_len[i] + R.h_ndel[i] : R.h_len[i];
-        R.h_rec_off[i + 1] = R.h_rec_off[i] + (int64_t)id.size() + count_digits(i + 1) + 1 + seqlen + 1;
-        max_len = std::max(max_len, R.h_len[i]);
-    }
-    R.out_bytes = R.h_rec_off[n_reads];
-    const size_t n1 = (size_t)std::max<int64_t>(n_reads, 1);
-    R.d_len.reserve(n1); R.d_ndel.reserve(n1); R.d_acc.reserve(n1); R.d_rec_off.reserve(n1 + 1);
-    R.d_dropped.reserve(n1); R.d_used.reserve(n1);
-    R.d_ctr.reserve(16);
-    R.d_out.reserve((size_t)R.out_bytes + 64, 0.05);
-    if (n_reads > 0) {
-        SP_CUDA(cudaMemcpyAsync(R.d_len.p, R.h_len.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
-        SP_CUDA(cudaMemcpyAsync(R.d_ndel.p, R.h_ndel.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
-        SP_CUDA(cudaMemcpyAsync(R.d_acc.p, R.h_acc.data(), n_reads, cudaMemcpyHostToDevice, st));
-    }
-    SP_CUDA(cudaMemcpyAsync(R.d_rec_off.p, R.h_rec_off.data(), (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
-    SP_CUDA(cudaMemsetAsync(R.d_ctr.p, 0, 64, st));
-    R.n_dropped = 0;
-    if (n_reads == 0) return;
+    if (!replay) {
+        // per-read streams: the plan is a map + scan + cut on the device, nothing but four scalars comes back
+        int64_t bases = 0, bytes = 0;
+        n_reads = plan_reads_on_device(c, R, ref_num, quota, (int32_t)id.size(), &max_len, &bases, &bytes);
+        R.n_reads = n_reads; R.ref_num = (long)ref_num; R.emitted_bases = bases; R.out_bytes = bytes;
+        R.plan_on_device = true;
+        const size_t n1 = (size_t)std::max<int64_t>(n_reads, 1);
+        R.d_dropped.reserve(n1); R.d_used.reserve(n1);
+        R.d_ctr.reserve(16);
+        R.d_out.reserve((size_t)R.out_bytes + 64, 0.05);
+        SP_CUDA(cudaMemsetAsync(R.d_ctr.p, 0, 64, st));
+        R.n_dropped = 0;
+        if (n_reads == 0) return;
+    } else {
+        R.plan_on_device = false;
+        long long len_total = 0;
+        std::vector<int32_t> first;  // two draws per read of the current batch
+        int64_t batch0 = 0, batch_n = 0;
+        auto fetch_batch = [&](int64_t r0) {
+            if (replay) {
+                batch0 = 0; batch_n = (int64_t)R.replay_off.size();
+                first.resize((size_t)batch_n * 2);
+                for (int64_t r = 0; r < batch_n; r++) {
+                    const int64_t o = R.replay_off[r];
+                    if (o < 0 || o + 1 >= (int64_t)R.replay_draws.size()) throw Error(SP_ERR_ARG, "replay: read offset outside the draw log");
+                    first[2 * r] = R.replay_draws[o]; first[2 * r + 1] = R.replay_draws[o + 1];
+                }
+                return;
+            }
+            const double mean_len = std::max(1.0, std::min(p.len_mean, (double)p.len_max));
+            int64_t n = (int64_t)((double)(quota - len_total) / mean_len * 1.05) + 1024;
+            n = std::min<int64_t>(n, 1 << 26);
+            R.d_first.reserve((size_t)n * 2);
+            first_draws_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(p.seed, ref_num, r0, n, R.d_first.p);
+            c->launches++;
+            SP_CUDA(cudaGetLastError());
+            first.resize((size_t)n * 2);
+            SP_CUDA(cudaMemcpyAsync(first.data(), R.d_first.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+            SP_CUDA(cudaStreamSynchronize(st));
+            batch0 = r0; batch_n = n;
+        };
+        int64_t r = 0;
+        while (len_total < quota) {  // :1641
+            if (r >= batch0 + batch_n) {
+                if (replay && batch_n > 0) throw Error(SP_ERR_ARG, "replay: the log has fewer reads than the quota needs");
+                fetch_batch(r);
+                if (batch_n == 0) throw Error(SP_ERR_ARG, "replay: empty log");
+            }
+            const long d0 = first[2 * (r - batch0)], d1 = first[2 * (r - batch0) + 1];
+            long len = t.prob2len[d0 % t.len_rand_value + 1];
+            if (len_total + len > quota) {
+                len = quota - len_total;
+                if (len < p.len_min) len = p.len_min;
+            }
+            const int accuracy = t.prob2accuracy[d1 % t.accuracy_rand_value + 1];
+            const long del_thre = int(((100 - accuracy) * p.del_rate) * 10000 + 0.5);      // :1682
+            const long del_num_total = int((float)len * del_thre / 1000000 + 0.5);         // :2282 (float32 product)
+            R.h_len.push_back((int32_t)len); R.h_acc.push_back((uint8_t)accuracy); R.h_ndel.push_back((int32_t)del_num_total);
+            len_total += len;  // strlen(mut.new_seq) == len whenever len' < ref.len (the kernel rejects the other case)
+            r++;
+        }
+        if (replay && r != (int64_t)R.replay_off.size())
+            throw Error(SP_ERR_ARG, "replay: the log has " + std::to_string(R.replay_off.size()) + " reads, the quota ends after " + std::to_string(r));
+        n_reads = r;
+        R.n_reads = n_reads; R.ref_num = (long)ref_num; R.emitted_bases = len_total;
+        // record offsets: ">" id_prefix ref_num "_" n "Z" seq "\n"
+        R.h_rec_off.assign((size_t)n_reads + 1, 0);
+        max_len = 2;
+        for (int64_t i = 0; i < n_reads; i++) {
+            const int64_t seqlen = p.no_error ? (int64_t)R.h_len[i] + R.h_ndel[i] : R.h_len[i];
+            R.h_rec_off[i + 1] = R.h_rec_off[i] + (int64_t)id.size() + count_digits(i + 1) + 1 + seqlen + 1;
+            max_len = std::max(max_len, R.h_len[i]);
+        }
+        R.out_bytes = R.h_rec_off[n_reads];
+        const size_t n1 = (size_t)std::max<int64_t>(n_reads, 1);
+        R.d_len.reserve(n1); R.d_ndel.reserve(n1); R.d_acc.reserve(n1); R.d_rec_off.reserve(n1 + 1);
+        R.d_dropped.reserve(n1); R.d_used.reserve(n1);
+        R.d_ctr.reserve(16);
+        R.d_out.reserve((size_t)R.out_bytes + 64, 0.05);
+        if (n_reads > 0) {
+            SP_CUDA(cudaMemcpyAsync(R.d_len.p, R.h_len.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
+            SP_CUDA(cudaMemcpyAsync(R.d_ndel.p, R.h_ndel.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
+            SP_CUDA(cudaMemcpyAsync(R.d_acc.p, R.h_acc.data(), n_reads, cudaMemcpyHostToDevice, st));
+        }
+        SP_CUDA(cudaMemcpyAsync(R.d_rec_off.p, R.h_rec_off.data(), (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
+        SP_CUDA(cudaMemsetAsync(R.d_ctr.p, 0, 64, st));
+        R.n_dropped = 0;
+        if (n_reads == 0) return;
 
-    // group the reads so that the 32 threads of a warp run nearly the same trip counts: longest first (tail balance),
-    // then by accuracy class (same tables, similar deletion loops). Counting sort, O(n).
-    {
-        const int32_t width = std::max(1, (max_len + 63) / 64);
-        std::vector<int32_t> count(64 * 101 + 1, 0);
-        auto key = [&](int64_t i) { return (63 - std::min(63, R.h_len[i] / width)) * 101 + (int)R.h_acc[i]; };
-        for (int64_t i = 0; i < n_reads; i++) count[key(i) + 1]++;
-        for (size_t k = 1; k < count.size(); k++) count[k] += count[k - 1];
-        R.h_order.resize((size_t)n_reads);
-        for (int64_t i = 0; i < n_reads; i++) R.h_order[(size_t)count[key(i)]++] = (int32_t)i;
-        R.d_order.reserve(n1);
-        SP_CUDA(cudaMemcpyAsync(R.d_order.p, R.h_order.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
+        // group the reads so that the 32 threads of a warp run nearly the same trip counts: longest first (tail balance),
+        // then by accuracy class (same tables, similar deletion loops). Counting sort, O(n).
+        {
+            const int32_t width = std::max(1, (max_len + 63) / 64);
+            std::vector<int32_t> count(64 * 101 + 1, 0);
+            auto key = [&](int64_t i) { return (63 - std::min(63, R.h_len[i] / width)) * 101 + (int)R.h_acc[i]; };
+            for (int64_t i = 0; i < n_reads; i++) count[key(i) + 1]++;
+            for (size_t k = 1; k < count.size(); k++) count[k] += count[k - 1];
+            R.h_order.resize((size_t)n_reads);
+            for (int64_t i = 0; i < n_reads; i++) R.h_order[(size_t)count[key(i)]++] = (int32_t)i;
+            R.d_order.reserve(n1);
+            SP_CUDA(cudaMemcpyAsync(R.d_order.p, R.h_order.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
+        }
     }
     int ctas_per_sm = 1;
     {   // Shared memory against L1: the generator state columns are 17 KB per CTA, but the table walks, the template
@@ -600,7 +771,7 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
         throw Error(SP_ERR_ARG, std::string("read kernel: ") + what[std::min<unsigned long long>(ctr[1], 3)] + ", read " + std::to_string(ctr[2] + 1));
     }
     R.n_dropped = (int64_t)ctr[3];
-    R.out_bytes = R.h_rec_off[n_reads] - (int64_t)ctr[4];
+    R.out_bytes -= (int64_t)ctr[4];
     if (replay) R.have_replay = false;
 }
 
@@ -624,6 +795,7 @@ static int64_t copy_reads(sp_ctx* c, uint8_t* host_out, int64_t capacity) {
     const uint8_t* src = R.d_out.p;
     if (R.n_dropped > 0) {
         fetch_read_log(c, R);
+        ensure_host_plan(c, R);
         std::vector<int64_t> koff((size_t)R.n_reads + 1, 0);
         for (int64_t r = 0; r < R.n_reads; r++)
             koff[r + 1] = koff[r] + (R.h_dropped[r] ? 0 : R.h_rec_off[r + 1] - R.h_rec_off[r]);
@@ -752,6 +924,7 @@ int sp_reads_log(sp_ctx* ctx, int32_t* length, uint8_t* dropped, uint32_t* draws
     SP_API_BEGIN
     sp::ReadState& R = sp::reads_of(ctx);
     sp::fetch_read_log(ctx, R);
+    sp::ensure_host_plan(ctx, R);
     const size_t n = (size_t)R.n_reads;
     if (length && n) memcpy(length, R.h_len.data(), n * 4);
     if (dropped && n) memcpy(dropped, R.h_dropped.data(), n);

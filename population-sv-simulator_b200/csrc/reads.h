@@ -84,6 +84,12 @@ struct ReadState {
     DevBuf<uint8_t> d_acc, d_dropped, d_out, d_scratch, d_seq, d_compact;
     DevBuf<int64_t> d_rec_off, d_replay_off, d_koff;
     DevBuf<uint32_t> d_used;
+    // per-read plan made on the device (per-read-stream mode): tables of simulate_by_model's loop header and work arrays
+    DevBuf<int32_t> d_prob2len, d_delthre, d_key, d_key2, d_idx;
+    DevBuf<uint8_t> d_prob2acc, d_cubtmp;
+    DevBuf<int64_t> d_len64, d_scan, d_reclen, d_planres;
+    bool plan_tables_stale = true;   // set by sp_reads_configure
+    bool plan_on_device = false;     // h_len / h_rec_off have not been fetched for the current batch
     DevBuf<int32_t> d_ctr;  // [0] work counter, [1] error code, [2] error read
     // device time of the last read kernel (CUDA events on the launching stream) and host time of the per-read plan
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
