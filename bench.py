@@ -151,6 +151,76 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
             "mix": mix_obj}
 
 
+def length_bins_leg(ctx, synth, work, peak, torch, cpu_baseline=True, genome=25_000_000, cov=30.0):
+    """Row D (SampleReadsFromLengthBins, src/SampleReadsFromLengthBins.java:19-81) with the bins resident in HBM: draws by
+    jump-ahead, in-bin ranks, cut at 2*coverage*genome bases, gather-copy of the records into one FASTQ (2 B per byte)."""
+    n_bins, bl = 70, 500
+    cum = synth.cumulative_bimodal(n_bins, bl, 9000, 1500, 15000, 2000, 0.3)
+    prob = np.diff(np.concatenate(([0.0], cum)))
+    target = int(genome * (cov * 2))
+    mean_len = float(sum(prob[b] * (b + 0.5) * bl for b in range(n_bins)))
+    per = [int(prob[b] * target / mean_len * 1.2) + 64 for b in range(n_bins)]
+    # synthetic bins in BuildReadLengthBins' format (4-line records, "@r" names), assembled from one random pool
+    rng = np.random.default_rng(7)
+    pool_n = 1 << 24
+    pool_seq = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=pool_n, dtype=np.uint8)]
+    pool_q = rng.integers(33 + 20, 33 + 60, size=pool_n).astype(np.uint8)
+    lens = [rng.integers(max(1, b * bl), (b + 1) * bl, size=per[b]) for b in range(n_bins)]
+    total = sum(int((2 * l + 7).sum()) for l in lens)
+    blob = np.empty(total, np.uint8)
+    off = np.zeros(n_bins + 1, np.int64)
+    head, mid = np.frombuffer(b"@r\n", np.uint8), np.frombuffer(b"\n+\n", np.uint8)
+    o = 0
+    for b in range(n_bins):
+        for ln in lens[b]:
+            ln = int(ln)
+            a = int(rng.integers(0, pool_n - ln))
+            blob[o:o + 3] = head; o += 3
+            blob[o:o + ln] = pool_seq[a:a + ln]; o += ln
+            blob[o:o + 3] = mid; o += 3
+            blob[o:o + ln] = pool_q[a:a + ln]; o += ln
+            blob[o] = 10; o += 1
+        off[b + 1] = o
+    ctx.length_bins_set(blob, off)
+    res = None
+    times = []
+    for it in range(4):   # first pass = warm-up (allocations)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = ctx.length_bins_sample(cum, target)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+        tm = ctx.length_bins_timing()
+    wall = min(times[1:])
+    achieved = 2.0 * res["fastq_bytes"] / (tm["copy_ms"] / 1e3) / 1e9
+    out = {"metric": "length-bin read Gbp/s", "value": res["bases"] / wall / 1e9, "unit": "Gbp/s",
+           "workload": f"SampleReadsFromLengthBins, 70 bins of 500 bp resident in HBM ({blob.nbytes} bytes), bimodal N(9000,1500)/N(15000,2000) "
+                       f"weight 0.3, genome {genome} bp, coverage {cov} per haplotype",
+           "reads": res["n_reads"], "bases": res["bases"], "fastq_bytes": res["fastq_bytes"], "attempts": res["attempts"],
+           "wall_s": wall, "sample_ms": tm["sample_ms"], "copy_ms": tm["copy_ms"],
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                        "kernel": "materialise_kernel (record gather)", "algorithmic_bytes_per_output_byte": 2.0}}
+    if cpu_baseline:
+        import oracle_helpers as oh
+        oh.ensure_oracle_built()
+        exe = os.path.join(ROOT, "oracle", "_build", "synthpop_oracle")
+        g2 = 2_000_000
+        prefix = os.path.join(work, "bins_")
+        synth.write_length_bins(prefix, n_bins, bl, [int(prob[b] * g2 * cov * 2 / mean_len * 1.3) + 8 for b in range(n_bins)], with_names=False)
+        cdf = os.path.join(work, "cdf.txt")
+        with open(cdf, "w") as f:
+            for v in cum:
+                f.write(repr(float(v)) + "\n")
+        argv = ["9000", "1500", "15000", "2000", "0.3", str(bl), str(n_bins * bl), prefix, str(g2), str(cov), os.path.join(work, "cpu.fastq")]
+        t0 = time.perf_counter()
+        rc = subprocess.run([exe, "--seed", "42", "--cdf", cdf, "SampleReadsFromLengthBins"] + argv, stderr=subprocess.DEVNULL).returncode
+        dt = time.perf_counter() - t0
+        if rc == 0:
+            out["cpu_baseline"] = {"value": g2 * cov * 2 / dt / 1e9, "unit": "Gbp/s", "cores": 1, "kind": "port",
+                                   "sample": f"CPU restatement of SampleReadsFromLengthBins.main (files on local disk), genome {g2} bp at {cov}x per haplotype in {dt:.1f} s"}
+    return out
+
+
 def reads_cpu_baseline(synth, work, L=1_500_000, depth=30):
     """The reference's own docker/pbsim2.cpp (compiled unmodified into oracle/_ref/pbsim2) on a bounded sample: one core,
     as the reference runs it (one pbsim process per haplotype)."""
@@ -269,6 +339,7 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="genotype/collision kernels on the materialisation stream")
     ap.add_argument("--read-haplotypes", type=int, default=2, help="haplotypes of the CCS read leg (0 = skip)")
     ap.add_argument("--read-depth", type=int, default=30)
+    ap.add_argument("--length-bins", type=int, default=1, help="row D leg (SampleReadsFromLengthBins), 0 = skip")
     ap.add_argument("--read-quality", default="phred", choices=["phred", "high"], help="emission centres of the synthetic HMM quality model")
     args = ap.parse_args()
 
@@ -418,6 +489,12 @@ def main():
             reads_obj["value"] = float(tb[0]) / float(tr[0]) / 1e9
             reads_obj["wall_s"] = float(tr[0])
 
+    # row D leg (rank 0 only: the same work would run on every GPU)
+    bins_obj = None
+    if args.length_bins and rank == 0:
+        peak, _ = measured_peak_gbs()
+        bins_obj = length_bins_leg(ctx, synth, work, peak, torch, cpu_baseline=(world == 1 and not args.no_cpu_baseline))
+
     # e2e: the reference-facing call with HOST buffers — reference + variant table + lists H2D, plan, materialise, D2H
     ne = args.e2e_haplotypes
     host_out = torch.empty(int((L + (4 << 20)) * max(ne, 1)) if ne > 0 else 16, dtype=torch.uint8, pin_memory=True)
@@ -465,6 +542,8 @@ def main():
                 "clocks": sampler.summary(), "wall_s_timed_region": t_wall}
         if reads_obj is not None:
             line["reads"] = reads_obj
+        if bins_obj is not None:
+            line["length_bins"] = bins_obj
         if world == 1 and not args.no_cpu_baseline:
             if reads_obj is not None:
                 rb = reads_cpu_baseline(synth, work)
