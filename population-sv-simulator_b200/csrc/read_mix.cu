@@ -317,19 +317,21 @@ int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const cha
     if (rc != SP_OK) return rc;
     if (output_file) {
         sp::ReadMixState& M = *ctx->mix;
-        FILE* f = fopen(output_file, "wb");
-        if (!f) throw Error(SP_ERR, std::string("cannot write ") + output_file);
+        struct Closer {  // the file and the pinned staging buffer are released on every path out of this block
+            FILE* f = nullptr;
+            uint8_t* stage = nullptr;
+            ~Closer() { if (f) fclose(f); if (stage) cudaFreeHost(stage); }
+        } io;
+        io.f = fopen(output_file, "wb");
+        if (!io.f) throw Error(SP_ERR, std::string("cannot write ") + output_file);
         const int64_t chunk = 256ll << 20;
-        uint8_t* stage = nullptr;
-        SP_CUDA(cudaMallocHost((void**)&stage, (size_t)std::min<int64_t>(chunk, std::max<int64_t>(M.out_bytes, 1))));
+        SP_CUDA(cudaMallocHost((void**)&io.stage, (size_t)std::min<int64_t>(chunk, std::max<int64_t>(M.out_bytes, 1))));
         for (int64_t o = 0; o < M.out_bytes; o += chunk) {
             const int64_t nb = std::min(chunk, M.out_bytes - o);
-            cudaMemcpyAsync(stage, M.d_out.p + o, (size_t)nb, cudaMemcpyDeviceToHost, ctx->stream);
-            cudaStreamSynchronize(ctx->stream);
-            if ((int64_t)fwrite(stage, 1, (size_t)nb, f) != nb) { fclose(f); cudaFreeHost(stage); throw Error(SP_ERR, "short write"); }
+            SP_CUDA(cudaMemcpyAsync(io.stage, M.d_out.p + o, (size_t)nb, cudaMemcpyDeviceToHost, ctx->stream));
+            SP_CUDA(cudaStreamSynchronize(ctx->stream));
+            if ((int64_t)fwrite(io.stage, 1, (size_t)nb, io.f) != nb) throw Error(SP_ERR, std::string("short write to ") + output_file);
         }
-        cudaFreeHost(stage);
-        fclose(f);
     }
     SP_API_END
 }
