@@ -138,18 +138,20 @@ __device__ __forceinline__ void job_error(const ReadJob& J, int code, int64_t r)
 
 // The oriented, upper-cased template (:2316-2341): seq[t] for t in [0, len'), fetched through aligned 8-byte chunks.
 // The strand is data (a step of +-1 and an xor mask), not a branch: the threads of a warp alternate strands.
+constexpr int LUT_REV_OFFSET = 288;  // bytes between the two strand tables (a shift of 8 banks: 'A' on one strand and
+                                     // 'A' on the other fall into different banks)
 struct Template {
     const unsigned long long* base8;  // 8-byte aligned address at or below seq[0]
     int32_t o0;                       // seq[0] - base8, 0..7
     int32_t dir;                      // +1 / -1
-    uint32_t rev;                     // 0 / 0xff
+    const uint8_t* lut;               // shared memory: byte -> upper-cased base (+) or its complement (-), :2316-2341
     int32_t cur;                      // index (relative to base8) of the cached 8-byte chunk
     uint32_t lo, hi;
-    __device__ __forceinline__ void begin(const uint8_t* w, int32_t lp, bool forward) {
+    __device__ __forceinline__ void begin(const uint8_t* w, int32_t lp, bool forward, const uint8_t* s_lut) {
         const uint8_t* origin = forward ? w : w + (lp - 1);  // first base of the window (+) or its last base (-)
         o0 = (int32_t)((uintptr_t)origin & 7);
         base8 = (const unsigned long long*)(origin - o0);
-        dir = forward ? 1 : -1; rev = forward ? 0u : 0xffu; cur = INT32_MIN; lo = hi = 0;
+        dir = forward ? 1 : -1; lut = forward ? s_lut : s_lut + LUT_REV_OFFSET; cur = INT32_MIN; lo = hi = 0;
     }
     __device__ __forceinline__ uint8_t at(int32_t t) {
         const int32_t rel = o0 + dir * t;   // 32-bit: a read is far shorter than 2^31 bases
@@ -158,11 +160,7 @@ struct Template {
             const unsigned long long chunk = __ldg(base8 + w);
             lo = (uint32_t)chunk; hi = (uint32_t)(chunk >> 32); cur = w;
         }
-        uint32_t c = __byte_perm(lo, hi, (uint32_t)(rel & 7)) & 0xffu;
-        c -= (c - 'a' <= 'z' - 'a') ? 32u : 0u;  // toupper
-        // complement: A(0x41)<->T(0x54) differ by 0x15, C(0x43)<->G(0x47) by 0x04; anything else stays
-        const uint32_t x = (c == 'A' || c == 'T') ? 0x15u : (c == 'C' || c == 'G') ? 0x04u : 0u;
-        return (uint8_t)(c ^ (x & rev));
+        return lut[__byte_perm(lo, hi, (uint32_t)(rel & 7)) & 0xffu];
     }
 };
 
@@ -305,7 +303,7 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     const uint32_t offset = bad ? 0u : S.next() % (uint32_t)(J.L - lenp + 1);
     const bool fwd = (r & 1) == 0;  // res_num % 2 == 0 before the increment (:2316)
     Template Tm;
-    Tm.begin(J.seq + offset, lenp, fwd);
+    Tm.begin(J.seq + offset, lenp, fwd, (const uint8_t*)(s_thre + 4 * PB_NQ));
     int64_t o = rec0;
     if (!bad) {  // ">S<ref>_<n>Z", a dozen bytes
         for (int i = 0; i < J.id_len; i++) J.out[o++] = (uint8_t)J.id[i];
@@ -382,10 +380,19 @@ template <bool REPLAY>
 __global__ void __launch_bounds__(RD_THREADS)
 reads_kernel(const ReadJob J, const ReadTablesDev T) {
     __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
-    __shared__ int32_t s_thre[4 * PB_NQ];  // err_thre, sub_thre, ins_thre, then max(err_thre[q..93])
+    __shared__ int32_t s_thre[4 * PB_NQ + (LUT_REV_OFFSET + 256) / 4];  // err_thre, sub_thre, ins_thre, max(err_thre[q..93]), strand tables
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 3 * PB_NQ; i += blockDim.x) s_thre[i] = T.thre[i];
     __syncthreads();
+    {   // toupper and toupper+complement (non-ACGT bytes keep their upper-cased value on both strands)
+        uint8_t* lut = (uint8_t*)(s_thre + 4 * PB_NQ);
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+            uint32_t ch = (uint32_t)i;
+            ch -= (ch - 'a' <= 'z' - 'a') ? 32u : 0u;
+            lut[i] = (uint8_t)ch;
+            lut[LUT_REV_OFFSET + i] = (uint8_t)(ch == 'A' ? 'T' : ch == 'T' ? 'A' : ch == 'C' ? 'G' : ch == 'G' ? 'C' : ch);
+        }
+    }
     if (threadIdx.x == 0) {
         int32_t m = 0;
         for (int q = PB_NQ - 1; q >= 0; q--) { m = max(m, s_thre[q]); s_thre[3 * PB_NQ + q] = m; }
