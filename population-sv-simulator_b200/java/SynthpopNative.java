@@ -23,6 +23,18 @@ final class SynthpopNative {
     static final MethodHandle sp_print_haplotypes = h("sp_print_haplotypes",
             FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     static final MethodHandle sp_sample_reads_from_bins = h("sp_sample_reads_from_bins", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    // the read path without intermediate files: docker/haplotype2reads.sh:53-64 and the coverage prefixes of reads2svs.sh:65-128
+    static final MethodHandle sp_load_reference_fasta = h("sp_load_reference_fasta", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle sp_load_population = h("sp_load_population", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    static final MethodHandle sp_reads_configure = h("sp_reads_configure", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle sp_haplotype2reads = h("sp_haplotype2reads",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_LONG, ADDRESS, ADDRESS, ADDRESS));
+    static final MethodHandle sp_reads_mix_coverage_prefix = h("sp_reads_mix_coverage_prefix",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    static final MethodHandle sp_reads_mix_copy = h("sp_reads_mix_copy", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, JAVA_LONG, ADDRESS));
+    // row T (extension): a Mendelian child of two simulated individuals
+    static final MethodHandle sp_trio_add_child = h("sp_trio_add_child",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT, JAVA_LONG, JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
 
     /** sp_population_args (include/synthpop_cuda.h): argv of SimulateHaplotypes.main, src/SimulateHaplotypes.java:76-86. */
     static final StructLayout POPULATION_ARGS = MemoryLayout.structLayout(
