@@ -286,14 +286,15 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
                 const int32_t v = (int32_t)(S.next() % 1000000u);
                 // v >= the largest threshold any position of this read can have: rejected whatever q[pos] is, and the
                 // scattered read of q[pos] (one HBM access for one byte) is not made. Same decision, same draws.
-                if (v >= tmax) continue;
-                const uint32_t sh = 8 * (pos & 3);
-                const int qv = (qw[(pos >> 2) * 32] >> sh) & 255u;
-                if (v < s_thre[qv]) {
-                    const uint32_t d = dw[(pos >> 2) * 32];
-                    if (((d >> sh) & 255u) == 255u) job_error(J, 3, r);
-                    dw[(pos >> 2) * 32] = d + (1u << sh);
-                    num++;
+                if (v < tmax) {   // (no `continue` here: every lane must reach the one vote instruction of this loop)
+                    const uint32_t sh = 8 * (pos & 3);
+                    const int qv = (qw[(pos >> 2) * 32] >> sh) & 255u;
+                    if (v < s_thre[qv]) {
+                        const uint32_t d = dw[(pos >> 2) * 32];
+                        if (((d >> sh) & 255u) == 255u) job_error(J, 3, r);
+                        dw[(pos >> 2) * 32] = d + (1u << sh);
+                        num++;
+                    }
                 }
             }
         }
