@@ -74,6 +74,18 @@ struct alignas(16) TileDesc {
     int64_t srcw;
     int32_t s0, nseg;
 };
+// Optional inline segment table of a tile with at most INLINE_SEGS segments (the record-gather uses of the copy kernel:
+// read mix, length bins): entry i of tile t lives at ((SegEntry*)(desc + ntiles))[t * INLINE_SEGS + i], so the copy kernel
+// can load it together with the descriptor instead of chasing seg_dst/seg_src afterwards. rel = first output byte of the
+// segment minus the tile's first byte (clamped to +-2^30), adj = source offset that corresponds to the tile's first byte.
+// A general tile whose entries were written has bit 40 of srcw set and rel of the segment after its last one in the low
+// 32 bits of srcw.
+struct alignas(16) SegEntry {
+    int32_t rel, kind;
+    int64_t adj;
+};
+constexpr int INLINE_SEGS = 8;
+constexpr int64_t TILE_INLINE_FLAG = int64_t(1) << 40;
 
 }  // namespace sp
 

@@ -412,7 +412,7 @@ static int sample_bins(sp_ctx* c, const double* cdf, int32_t n_bins, int64_t tar
     const int64_t stride = (B.out_bytes + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES;
     B.d_seg_dst.reserve(nseg); B.d_seg_src.reserve(nseg); B.d_seg_base.reserve(2);
     B.d_hdr.reserve((size_t)header_bytes_before(B.n_reads) + 64);
-    B.d_tile_first.reserve(stride / TILE_BYTES);
+    B.d_tile_first.reserve((stride / TILE_BYTES) * (1 + INLINE_SEGS));  // descriptors + inline segment entries
     B.d_out.reserve((size_t)stride, 0.02);
     const int64_t seg_base[2] = {0, nseg};
     SP_CUDA(cudaMemcpyAsync(B.d_seg_base.p, seg_base, sizeof seg_base, cudaMemcpyHostToDevice, st));

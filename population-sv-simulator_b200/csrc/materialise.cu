@@ -143,7 +143,7 @@ plan_kernel(const int8_t* __restrict__ type, const int32_t* __restrict__ pos, co
 // data loads instead of a chain through tile_first -> seg_dst/seg_src.
 __global__ void __launch_bounds__(256)
 tile_table_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
-                  int n_hap, int64_t tiles_per_slot, TileDesc* __restrict__ desc) {
+                  int n_hap, int64_t tiles_per_slot, TileDesc* __restrict__ desc, int inline_entries) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= tiles_per_slot * n_hap) return;
     const int hb = (int)(idx / tiles_per_slot);
@@ -172,6 +172,20 @@ tile_table_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict
     } else {
         d.nseg = (int32_t)(s1 - s0 + 1);
         d.srcw = 0;
+        if (inline_entries && d.nseg <= INLINE_SEGS) {
+            auto clamp = [](int64_t r) { return (int32_t)(r < -(1 << 30) ? -(1 << 30) : (r > (1 << 30) ? (1 << 30) : r)); };
+            SegEntry* e = (SegEntry*)(desc + tiles_per_slot * n_hap) + idx * INLINE_SEGS;
+            for (int i = 0; i < d.nseg; i++) {
+                const int64_t r = seg_dst[sb + s0 + i] - x;
+                const int64_t sw = seg_src[sb + s0 + i];
+                const int k = (int)(sw >> SEG_KIND_SHIFT);
+                SegEntry v;
+                v.rel = clamp(r); v.kind = k;
+                v.adj = k == SEG_REF_RC ? (sw & SEG_OFF_MASK) + r : (sw & SEG_OFF_MASK) - r;
+                e[i] = v;
+            }
+            d.srcw = TILE_INLINE_FLAG | (int64_t)(uint32_t)clamp(seg_dst[sb + s0 + d.nseg] - x);
+        }
     }
     desc[idx] = d;
 }
@@ -231,13 +245,19 @@ materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ 
                    const uint8_t* __restrict__ aux, const int64_t* __restrict__ seg_dst,
                    const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
                    const TileDesc* __restrict__ desc, uint8_t* __restrict__ out, int64_t stride,
-                   int64_t tiles_per_slot, int n_hap) {
+                   int64_t tiles_per_slot, int n_hap, int inline_entries) {
     // region-major order: consecutive CTAs work on the same tile index of different haplotypes
     const int64_t b = blockIdx.x;
     const int hb = (int)(b % n_hap);
     const int64_t t = b / n_hap;
     const int64_t x0 = t * TILE_BYTES;
-    const int4 dw = __ldg((const int4*)(desc + ((int64_t)hb * tiles_per_slot + t)));
+    const int64_t tile = (int64_t)hb * tiles_per_slot + t;
+    const int4 dw = __ldg((const int4*)(desc + tile));
+    // record-gather launches: nearly every tile is crossed by record boundaries, so the tile's inline segment entries are
+    // requested together with the descriptor (one memory round trip before the data loads instead of two)
+    int4 ev = make_int4(0, 0, 0, 0);
+    if (inline_entries && threadIdx.x < INLINE_SEGS)
+        ev = __ldg((const int4*)((const SegEntry*)(desc + tiles_per_slot * n_hap) + tile * INLINE_SEGS + threadIdx.x));
     uint8_t* __restrict__ dst_tile = out + (int64_t)hb * stride + x0;
     const int tid = threadIdx.x;
     constexpr int CH = TILE_BYTES / 16 / 256;
@@ -281,6 +301,11 @@ materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ 
     __shared__ int32_t s_rel[MAX_TILE_SEGS + 1];
     __shared__ int64_t s_adj[MAX_TILE_SEGS];
     __shared__ int32_t s_kind[MAX_TILE_SEGS];
+    const int64_t srcw = ((int64_t)(uint32_t)dw.y << 32) | (uint32_t)dw.x;
+    if (inline_entries && (srcw & TILE_INLINE_FLAG)) {
+        if (tid < nseg) { s_rel[tid] = ev.x; s_kind[tid] = ev.y; s_adj[tid] = ((int64_t)(uint32_t)ev.w << 32) | (uint32_t)ev.z; }
+        if (tid == 0) s_rel[nseg] = (int32_t)(uint32_t)dw.x;
+    } else
     for (int i = tid; i <= nseg; i += 256) {
         const int64_t r = seg_dst[sb + i] - x0;
         s_rel[i] = (int32_t)(r < -(1 << 30) ? -(1 << 30) : (r > (1 << 30) ? (1 << 30) : r));
@@ -370,8 +395,8 @@ static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
 static void launch_materialise(cudaStream_t st, int64_t ntiles, const uint8_t* ref, const uint8_t* payload, const uint8_t* aux,
                                const int64_t* seg_dst, const int64_t* seg_src, const int64_t* seg_base, const TileDesc* desc,
-                               uint8_t* out, int64_t stride, int64_t tiles_per_slot, int n_slots) {
-    materialise_kernel<<<(unsigned)ntiles, 256, 0, st>>>(ref, payload, aux, seg_dst, seg_src, seg_base, desc, out, stride, tiles_per_slot, n_slots);
+                               uint8_t* out, int64_t stride, int64_t tiles_per_slot, int n_slots, int inline_entries) {
+    materialise_kernel<<<(unsigned)ntiles, 256, 0, st>>>(ref, payload, aux, seg_dst, seg_src, seg_base, desc, out, stride, tiles_per_slot, n_slots, inline_entries);
 }
 
 void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride) {
@@ -436,7 +461,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "batch too large: reduce the haplotype range");
     c->d_tile_desc.reserve(ntiles);
     tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(c->d_seg_dst.p, c->d_seg_src.p, c->d_seg_base.p, nh,
-                                                                        c->tiles_per_slot, c->d_tile_desc.p);
+                                                                        c->tiles_per_slot, c->d_tile_desc.p, 0);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     c->d_out.reserve((size_t)c->slot_stride * nh, 0.01);
@@ -450,7 +475,7 @@ void materialise(sp_ctx* c) {
     const int nh = c->plan_last - c->plan_first + 1;
     const int64_t ntiles = c->tiles_per_slot * nh;
     launch_materialise(c->stream, ntiles, c->d_ref.p, c->d_payload.p, c->d_aux.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_seg_base.p,
-                       c->d_tile_desc.p, c->d_out.p, c->slot_stride, c->tiles_per_slot, nh);
+                       c->d_tile_desc.p, c->d_out.p, c->slot_stride, c->tiles_per_slot, nh, 0);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     c->materialised = true;
@@ -466,8 +491,9 @@ void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, co
     const int64_t ntiles = tiles_per_slot * n_slots;
     if (ntiles <= 0) return;
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "tiled copy: too many tiles");
-    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, c->stream>>>(seg_dst, seg_src, seg_base, n_slots, tiles_per_slot, tile_desc);
-    launch_materialise(c->stream, ntiles, src, payload, aux, seg_dst, seg_src, seg_base, tile_desc, out, stride, tiles_per_slot, n_slots);
+    // tile_desc holds ntiles descriptors followed by ntiles * INLINE_SEGS inline segment entries (both 16 bytes each)
+    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, c->stream>>>(seg_dst, seg_src, seg_base, n_slots, tiles_per_slot, tile_desc, 1);
+    launch_materialise(c->stream, ntiles, src, payload, aux, seg_dst, seg_src, seg_base, tile_desc, out, stride, tiles_per_slot, n_slots, 1);
     c->launches += 2;
     SP_CUDA(cudaGetLastError());
 }

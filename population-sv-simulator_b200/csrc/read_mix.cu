@@ -157,7 +157,7 @@ static void mix_finish(sp_ctx* c, int64_t shuffle_seed) {
     M.out_bytes = A.bytes + (M.n_sources > 1 ? B.bytes : 0);
     for (auto& e : M.ev) if (!e) SP_CUDA(cudaEventCreate(&e));
     const int64_t stride = std::max<int64_t>(TILE_BYTES, (M.out_bytes + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES);
-    M.d_tile_first.reserve((size_t)(stride / TILE_BYTES));
+    M.d_tile_first.reserve((size_t)(stride / TILE_BYTES) * (1 + INLINE_SEGS));  // descriptors + inline segment entries
     M.d_out.reserve((size_t)stride, 0.02);
     SP_CUDA(cudaEventRecord(M.ev[0], st));
     const size_t n1s = (size_t)std::max<int64_t>(n, 1);
