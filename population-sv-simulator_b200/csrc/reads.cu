@@ -5,7 +5,7 @@
 // order (Appendix A.6): quality chain, deletion rejection loop, start offset, then one draw per base plus 1-2 per
 // error event. The work per base is a few dozen dependent integer operations and no reuse, so the design is
 // ONE THREAD PER READ (first version: one warp per read around a shared-memory draw ring — 16 warp instructions per
-// base, most of them cooperation overhead; see profiles/r01_reads_kernel.md):
+// base, most of them cooperation overhead; see profiles/r01_reads_kernel_v1_lines.txt .. r01c_reads_kernel_lines.txt):
 //   * the thread runs the reference's loops as they are, with the glibc TYPE_3 generator r[i] = r[i-31] + r[i-3] as
 //     a 31-word circular buffer in shared memory laid out [word][thread] (bank = thread: conflict-free whatever
 //     each thread's phase), one add per draw;
@@ -14,6 +14,12 @@
 //   * per-read scratch (quality codes and deletion counters, one byte per position) lives in HBM interleaved
 //     [word][lane], so the sequential passes are 128-byte coalesced and only the rejection loop's lookups scatter;
 //   * the haplotype window is read in aligned 8-byte chunks and the read is written in aligned 8-byte chunks.
+//   * the quality loops are unrolled by 31 bases: every read enters them after the same number of draws, so the ring
+//     position of each quality draw is a compile-time constant there;
+//   * the deletion rejection loop skips the scattered lookup of q[pos] whenever the draw is already above the largest
+//     threshold any position of the read can have (same decisions, same draws);
+//   * in per-read-stream mode the loop header (length, accuracy, quota cut, record offsets, work order) is computed on
+//     the device as map + scan + cut (plan_*_kernel), the host only learns four scalars.
 // Replay mode feeds the same code from the reference's logged draws instead of the generator.
 // Everything is integer arithmetic; the only floating-point expressions of the reference's loop (:1682, :2282) are
 // evaluated on the host with the reference's own types when the per-read plan is made.
