@@ -383,8 +383,9 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     }
 }
 
+// 10 CTAs per SM (48 registers, a few spilled words): measured best against 8, 9 and 12 with the default carve-out
 template <bool REPLAY>
-__global__ void __launch_bounds__(RD_THREADS)
+__global__ void __launch_bounds__(RD_THREADS, 10)
 reads_kernel(const ReadJob J, const ReadTablesDev T) {
     __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
     __shared__ int32_t s_thre[4 * PB_NQ + (LUT_REV_OFFSET + 256) / 4];  // err_thre, sub_thre, ins_thre, max(err_thre[q..93]), strand tables
