@@ -140,6 +140,18 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
                    "copy_GBps_algorithmic": 2.0 * mixed_bytes / (mt["copy_ms"] / 1e3) / 1e9, "copy_frac_of_peak": 2.0 * mixed_bytes / (mt["copy_ms"] / 1e3) / 1e9 / peak,
                    "coverage_prefix_bytes": sweep}
     achieved = READ_ALGO_BYTES_PER_BASE * bases / (k_ms / 1e3) / 1e9
+    # the bound that applies: warp instructions issued per second against 4 per clock per SM, with the
+    # instructions per base of the committed ncu capture
+    issue = None
+    tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tp):
+        ipb = json.load(open(tp)).get("reads_kernel", {}).get("warp_instructions_per_base")
+        if ipb:
+            props = torch.cuda.get_device_properties(torch.cuda.current_device())
+            peak_issue = props.multi_processor_count * 4 * 1.965e9
+            rate = ipb * bases / (k_ms / 1e3)
+            issue = {"bound": "issue", "achieved": rate / 1e12, "peak": peak_issue / 1e12, "unit": "T warp-inst/s",
+                     "frac": rate / peak_issue, "warp_instructions_per_base": ipb, "note": "peak = SMs x 4 schedulers x 1965 MHz"}
     return {"metric": "CCS read Gbp/s", "value": bases / dt / 1e9, "unit": "Gbp/s",
             "workload": f"pbsim2 model mode, {depth}x over {n_haps} materialised chr1-sized haplotypes, length 15000+-2000 in [5000,30000], "
                         f"accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model ({quality} emission centres), per-read glibc streams",
@@ -148,7 +160,7 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
             "kernel_gbp_s": bases / (k_ms / 1e3) / 1e9, "gpu_launches": ctx.kernel_launches - l0,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE},
-            "mix": mix_obj}
+            "issue_roofline": issue, "mix": mix_obj}
 
 
 def length_bins_leg(ctx, synth, work, peak, torch, cpu_baseline=True, genome=25_000_000, cov=30.0):
