@@ -44,3 +44,16 @@ def test_print_haplotypes_and_haplotype2reads_commands(oracle_bin, oracle_lib, t
         w, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=11, per_read_streams=True, ref_num=1, **p)
         recs.append(w.tobytes())
     assert open(out, "rb").read() == rm.mix_reads(recs, 11)
+
+
+def test_whole_genome_driver_small(tmp_path):
+    """tools/whole_genome.py (BASELINE config 3) at 0.4 % scale: three chromosomes, rank 1 of 2 owns individuals 4..7."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "whole_genome.py"), "--scale", "0.004", "--chromosomes", "3",
+                        "--individuals", "8", "--as-world", "2", "--as-rank", "1"], capture_output=True, check=True, timeout=300)
+    line = json.loads(r.stdout.decode().strip().splitlines()[-1])
+    rows = line["chromosomes"]
+    assert [c["chromosome"] for c in rows] == ["chr1", "chr2", "chr3"]
+    assert all(c["haplotypes"] == 8 and c["variants"] > 0 for c in rows)
+    assert line["bases"] == sum(c["bases"] for c in rows) and line["gpu_launches"] > 0
+    assert all(c["bases"] > 0 and c["copy_ms"] > 0 for c in rows)
