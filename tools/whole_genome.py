@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--as-rank", type=int, default=0)
     ap.add_argument("--scale", type=float, default=1.0, help="shrink every chromosome (smoke runs)")
     ap.add_argument("--chromosomes", type=int, default=len(GRCH38))
+    ap.add_argument("--only", default="", help="comma-separated chromosome names (profiling one launch shape)")
     ap.add_argument("--repeats", type=int, default=3, help="materialisation passes per chromosome (first is warm-up)")
     args = ap.parse_args()
 
@@ -61,7 +62,10 @@ def main():
     bases_total = 0
     t_gen_total = t_pop_total = 0.0
     launches = 0
+    only = set(filter(None, args.only.split(",")))
     for name, full in GRCH38[: args.chromosomes]:
+        if only and name not in only:
+            continue
         L = max(200_000, int(full * args.scale))
         work = tempfile.mkdtemp(prefix=f"synthpop_wg_r{rank}_")
         try:
