@@ -234,9 +234,16 @@ int sp_reads_mix_device(sp_ctx* ctx, void** file_bytes, void** read_offsets, int
 int sp_reads_mix_offsets(sp_ctx* ctx, int64_t* read_offsets);
 /* Device time of the last finish: ordering (keys, sort, scans, segment table) and the tiled copy. */
 int sp_reads_mix_timing(sp_ctx* ctx, double* order_ms, double* copy_ms);
+/* The pbsim seed sp_haplotype2reads uses for haplotype `haplotype` when sp_reads_configure was given `seed`. The reference
+ * runs one pbsim PROCESS per haplotype, each seeded with its own time(NULL) (docker/pbsim2.cpp:191,
+ * docker/haplotype2reads.sh:53-58): the two haplotypes of an individual, the individuals of a cohort and a child and its
+ * parents all get independent sequencing errors and coverage fluctuations. Here that independence comes from this pure
+ * function (splitmix64 finaliser of seed and haplotype id, mapped to [1, 2^31-2]); ref_num stays 1 so the record names
+ * match the reference's. */
+uint32_t sp_haplotype_read_seed(uint32_t seed, int32_t haplotype);
 /* docker/haplotype2reads.sh:53-64 for the individual with haplotypes id1 and id1+1 (sp_reads_configure holds the pbsim
- * options): materialise both, pbsim on each (ref_num 1, as each is its own process there), mix, write output_file
- * (NULL = keep it on the device only). */
+ * options): materialise both, pbsim on each (ref_num 1, as each is its own process there; seed
+ * sp_haplotype_read_seed(seed, h) for haplotype h), mix, write output_file (NULL = keep it on the device only). */
 int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const char* output_file, int64_t* n_reads,
                        int64_t* file_bytes);
 
@@ -268,6 +275,29 @@ int sp_length_bins_sample(sp_ctx* ctx, const double* cumulative, int32_t n_bins,
 int sp_length_bins_copy(sp_ctx* ctx, uint8_t* host_out, int64_t capacity, int64_t* written);
 /* Device milliseconds of the last sample call: draw/rank/scan/emit kernels, and the tiled gather-copy. */
 int sp_length_bins_timing(sp_ctx* ctx, double* sample_ms, double* copy_ms);
+
+/* ---- AnnotateVCF ------------------------------------------------------------------------------ */
+/* Positional argv of AnnotateVCF.main (src/AnnotateVCF.java:96-102). Every DEL/DUP/INS/INV record of every listed VCF gets
+ * ";REPEATS_START=t;REPEATS_END=t;REPEATS_FRACTION=x.xxxx" appended to INFO (:195); other lines are copied. Output file =
+ * the input path up to its first ".vcf" + "_annotated.vcf" (:119). */
+typedef struct sp_annotate_args {
+    const char* input_files_list;       /* args[0]: one VCF path per line */
+    int32_t min_distance;               /* args[1] */
+    int32_t max_distance;               /* args[2] */
+    const char* reference_file;         /* args[3] */
+    const char* repeat_intervals_file;  /* args[4] */
+    const char* segdups_file;           /* args[5] */
+} sp_annotate_args;
+int sp_annotate_vcf(sp_ctx* ctx, const sp_annotate_args* args);
+/* The same in steps. load = :112-115 (loadReference, deserializeRepeatIntervals, deserializeSegdups, loadPositions): the five
+ * repeat-context position sets go to HBM as sorted disjoint intervals with prefix counts. file = annotateVCF (:127-205) for
+ * one VCF: the host parses the text, one GPU thread per record answers getRepeatType (:437-457) twice and getRepeatSurface
+ * (:480-495) by rank queries. n_annotated (may be NULL) = records that received the three fields. */
+int sp_annotate_load(sp_ctx* ctx, const char* reference_file, const char* repeat_intervals_file, const char* segdups_file);
+int sp_annotate_file(sp_ctx* ctx, const char* input_vcf, const char* output_vcf, int32_t min_distance, int32_t max_distance,
+                     int64_t* n_annotated);
+/* Seconds of the last load, device milliseconds of the last file's kernel, records annotated since the load. */
+int sp_annotate_timing(sp_ctx* ctx, double* load_seconds, double* last_kernel_ms, int64_t* records_total);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,6 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY. Command-line front end of the CPU restatement:
 //   synthpop_oracle [--seed S] [--quiet] [--dump-pre-collision FILE] [--draw-log FILE] [--cdf FILE]
-//                   <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins> <positional argv of the Java class>
+//                   <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF> <positional argv of the Java class>
 // Exit codes follow the Java: 0 ok, 1 uncaught exception, 3 = SampleReadsFromLengthBins coverage unreachable.
 // The seed replaces the reference's unseeded `new Random()` (src/SimulateHaplotypes.java:71) — the one
 // documented deviation from the reference argv (SURVEY.md §8b "Seed").
@@ -8,6 +8,7 @@
 
 namespace oracle {
 int sampleReadsFromLengthBinsMain(const std::vector<std::string>& args, int64_t seed, const std::string& cdfFile);
+int annotateVcfMain(const std::vector<std::string>& args);
 }
 
 int main(int argc, char** argv) {
@@ -55,6 +56,8 @@ int main(int argc, char** argv) {
             return sh.mainPrint(args);
         } else if (cls == "SampleReadsFromLengthBins") {
             return oracle::sampleReadsFromLengthBinsMain(args, seed, cdfFile);
+        } else if (cls == "AnnotateVCF") {
+            return oracle::annotateVcfMain(args);
         }
         fprintf(stderr, "unknown class %s\n", cls.c_str());
         return 2;

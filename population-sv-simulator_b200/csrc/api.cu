@@ -10,6 +10,7 @@ void free_population(sp_ctx* c);
 void free_reads(sp_ctx* c);
 void free_length_bins(sp_ctx* c);
 void free_read_mix(sp_ctx* c);
+void free_annotate(sp_ctx* c);
 
 std::string java_double_to_string(double d) {
     if (d != d) return "NaN";
@@ -192,11 +193,6 @@ static void check_planned(sp_ctx* c, int32_t h) {
 
 using sp::Error;
 
-#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { cudaSetDevice(ctx->device);
-#define SP_API_END                                                                         \
-    return SP_OK; }                                                                        \
-    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
-    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }
 
 extern "C" {
 
@@ -228,7 +224,10 @@ void sp_destroy(sp_ctx* ctx) {
     sp::free_reads(ctx);
     sp::free_length_bins(ctx);
     sp::free_read_mix(ctx);
-    if (ctx->ev_plan) cudaEventDestroy(ctx->ev_plan);
+    sp::free_annotate(ctx);
+    if (ctx->ev_planned) cudaEventDestroy(ctx->ev_planned);
+    for (auto& b : ctx->plan_set) if (b.ev_used) cudaEventDestroy(b.ev_used);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     delete ctx;
     if (s) cudaStreamDestroy(s);
 }
@@ -244,7 +243,6 @@ int sp_set_stream(sp_ctx* ctx, void* cuda_stream) {
 int sp_set_population_stream(sp_ctx* ctx, void* cuda_stream) {
     SP_API_BEGIN
     ctx->pop_stream = (cudaStream_t)cuda_stream;
-    if (cuda_stream && !ctx->ev_plan) SP_CUDA(cudaEventCreateWithFlags(&ctx->ev_plan, cudaEventDisableTiming));
     SP_API_END
 }
 
@@ -259,7 +257,9 @@ int sp_load_reference_fasta(sp_ctx* ctx, const char* path) {
 int sp_set_reference(sp_ctx* ctx, const uint8_t* bases, int64_t length) {
     SP_API_BEGIN
     if (length < 0 || (length > 0 && !bases) || length > INT32_MAX) throw Error(SP_ERR_ARG, "bad reference buffer");
-    // straight H2D from the caller's (ideally pinned) buffer; no host copy is kept
+    // straight H2D from the caller's (ideally pinned) buffer; no host copy is kept. A population begun on the previous
+    // reference is dropped: its writers would read the host copy that is no longer there.
+    sp::free_population(ctx);
     ctx->h_ref.clear();
     ctx->ref_len = length;
     ctx->d_ref.reserve(std::max<size_t>((size_t)length, 1));
@@ -275,6 +275,7 @@ int sp_set_variants(sp_ctx* ctx, int32_t n, const int8_t* sv_type, const int32_t
                     const int64_t* payload_off, const uint8_t* payload_blob, const int8_t* has_payload) {
     SP_API_BEGIN
     if (n < 0 || (n > 0 && (!sv_type || !position || !length))) throw Error(SP_ERR_ARG, "bad variant table");
+    sp::free_population(ctx);   // its tables are being replaced
     ctx->n_variants = n;
     ctx->h_type.assign(sv_type, sv_type + n);
     ctx->h_pos.assign(position, position + n);
@@ -299,6 +300,7 @@ int sp_set_haplotype_lists(sp_ctx* ctx, int32_t n_haplotypes, const int64_t* lis
     if (n_haplotypes < 0 || !list_off || list_off[0] != 0) throw Error(SP_ERR_ARG, "bad haplotype lists");
     for (int32_t i = 0; i < n_haplotypes; i++)
         if (list_off[i + 1] < list_off[i]) throw Error(SP_ERR_ARG, "list offsets must be non-decreasing");
+    sp::free_population(ctx);   // its lists are being replaced
     ctx->n_haplotypes = n_haplotypes;
     ctx->h_list_off.assign(list_off, list_off + n_haplotypes + 1);
     ctx->h_list_ids.assign(ids, ids + list_off[n_haplotypes]);

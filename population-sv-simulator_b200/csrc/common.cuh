@@ -15,6 +15,8 @@ struct PopulationState;
 struct ReadState;
 struct LengthBinState;
 struct ReadMixState;
+struct AnnotateState;
+struct LengthBinBuilderState;
 
 struct Error : std::runtime_error {
     int code;
@@ -96,8 +98,10 @@ struct sp_ctx {
     cudaStream_t stream = nullptr;
     // optional second stream for rows G/C/N (sp_set_population_stream): the genotype kernels and the serial collision
     // fixer of batch s+1 then run under the materialisation kernel of batch s
+    // The plan (segment scan, tile table) of a batch is issued on the same second stream, into the plan set the copy kernel
+    // of the batch before is NOT reading, so the host round trip that sizes the slots never waits behind a copy kernel.
     cudaStream_t pop_stream = nullptr;
-    cudaEvent_t ev_plan = nullptr;   // recorded after plan_kernel has consumed the lists of the current batch
+    cudaEvent_t ev_planned = nullptr;   // recorded on the planning stream after tile_table_kernel of the current plan
     std::string err;
     int64_t launches = 0;
     int sm_count = 148;
@@ -139,10 +143,26 @@ struct sp_ctx {
     int64_t tiles_per_slot = 0;
     std::vector<int64_t> h_hap_len;      // framed lengths
     std::vector<int32_t> h_hdr_len;      // header bytes preceding the sequence in each slot
-    sp::DevBuf<int64_t> d_seg_dst, d_seg_src, d_seg_base, d_hap_len;
-    sp::DevBuf<sp::TileDesc> d_tile_desc;
-    sp::DevBuf<uint8_t> d_aux;
-    sp::DevBuf<int64_t> d_aux_off;
+    struct PlanSet {   // everything sp_materialise reads besides the reference, the payloads and the slots
+        sp::DevBuf<int64_t> seg_dst, seg_src, seg_base, aux_off;
+        sp::DevBuf<sp::TileDesc> tile_desc;
+        sp::DevBuf<uint8_t> aux;
+        cudaEvent_t ev_used = nullptr;   // recorded on the materialisation stream after the last copy kernel that read this set
+    } plan_set[2];
+    int plan_cur = 0;
+    sp::DevBuf<int64_t> d_hap_len;
+    int64_t* h_pinned = nullptr;         // small pinned staging area for the size read-backs (plan, rows G/C/N)
+    size_t h_pinned_bytes = 0;
+    int64_t* pinned(size_t bytes) {
+        if (bytes > h_pinned_bytes) {
+            if (h_pinned) cudaFreeHost(h_pinned);
+            h_pinned = nullptr; h_pinned_bytes = 0;
+            const size_t want = bytes < (1u << 16) ? (1u << 16) : bytes * 2;
+            if (cudaHostAlloc((void**)&h_pinned, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); throw sp::Error(SP_ERR_CUDA, "cudaHostAlloc of the read-back staging area failed"); }
+            h_pinned_bytes = want;
+        }
+        return h_pinned;
+    }
     sp::DevBuf<int32_t> d_err;
     sp::DevBuf<uint8_t> d_out;
     bool materialised = false;
@@ -158,4 +178,14 @@ struct sp_ctx {
 
     // §8(f) rank 1: the tail of docker/haplotype2reads.sh (cat, shuf, tr) and the coverage chunks of reads2svs.sh
     sp::ReadMixState* mix = nullptr;
+
+    // §8(f) rank 2: AnnotateVCF (row A3's interval sets resident in HBM)
+    sp::AnnotateState* annot = nullptr;
 };
+
+// Entry/exit of every extern "C" function: bind the context's device (failing loudly), turn exceptions into codes.
+#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { SP_CUDA(cudaSetDevice(ctx->device));
+#define SP_API_END                                                                         \
+    return SP_OK; }                                                                        \
+    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
+    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }

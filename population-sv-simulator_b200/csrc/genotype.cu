@@ -55,15 +55,17 @@ count_bits_kernel(const uint32_t* __restrict__ bits, int32_t W, int32_t* __restr
 
 // Exclusive scan of int32 counts into int64 offsets (n+1 entries), single CTA.
 __global__ void __launch_bounds__(1024)
-scan_counts_kernel(const int32_t* __restrict__ cnt, int32_t n, int64_t* __restrict__ off) {
+scan_counts_kernel(const int32_t* __restrict__ cnt, int32_t n, int64_t* __restrict__ off, int32_t* __restrict__ max_out = nullptr) {
     __shared__ int64_t ws[32];
     __shared__ int64_t carry;
-    if (threadIdx.x == 0) carry = 0;
+    __shared__ int32_t mx_s;
+    if (threadIdx.x == 0) { carry = 0; mx_s = 0; }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int32_t base = 0; base < n; base += 1024) {
         const int32_t k = base + threadIdx.x;
         const int64_t v = k < n ? cnt[k] : 0;
+        if (max_out && v > 0) atomicMax(&mx_s, (int32_t)v);
         int64_t incl = v;
         for (int d = 1; d < 32; d <<= 1) {
             const int64_t o = __shfl_up_sync(0xffffffffu, incl, d);
@@ -78,7 +80,7 @@ scan_counts_kernel(const int32_t* __restrict__ cnt, int32_t n, int64_t* __restri
         if (threadIdx.x == 0) carry += tot;
         __syncthreads();
     }
-    if (threadIdx.x == 0) off[n] = carry;
+    if (threadIdx.x == 0) { off[n] = carry; if (max_out) *max_out = mx_s; }
 }
 
 __global__ void __launch_bounds__(256)
@@ -454,17 +456,36 @@ compact_count_kernel(const int64_t* __restrict__ off, const int32_t* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------------ host
-void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
+// Host copies of the local lists and carrier counts: only the writers and the list getters need them, a batch that goes
+// straight from rows G/C/N to the plan kernel never moves them off the device.
+void fetch_host_lists(sp_ctx* c, PopulationState& P) {
+    if (P.host_lists_valid) return;
     cudaStream_t st = c->pop_stream ? c->pop_stream : c->stream;
-    // the lists of the previous batch are free once its plan_kernel has read them
-    if (c->pop_stream && c->ev_plan) SP_CUDA(cudaStreamWaitEvent(st, c->ev_plan, 0));
+    const int32_t V = P.n_variants, Hl = P.h1 - P.h0;
+    P.h_ids.assign((size_t)P.h_off[Hl], 0);
+    if (P.h_off[Hl] > 0) SP_CUDA(cudaMemcpyAsync(P.h_ids.data(), P.d_ids2.p, (size_t)P.h_off[Hl] * 4, cudaMemcpyDeviceToHost, st));
+    P.h_counts_local.assign(V, 0);
+    if (V > 0) SP_CUDA(cudaMemcpyAsync(P.h_counts_local.data(), P.d_counts.p, (size_t)V * 4, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaStreamSynchronize(st));
+    P.host_lists_valid = true;
+}
+
+void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
+    // On the planning stream when there is one (sp_set_population_stream): the plan kernel that read the previous batch's
+    // lists ran on the same stream, so they are free to be overwritten in stream order.
+    cudaStream_t st = c->pop_stream ? c->pop_stream : c->stream;
     const int32_t V = P.n_variants, H = P.n_haplotypes_total, h0 = P.h0, Hl = P.h1 - P.h0;
     const int32_t W = (V + 31) / 32;
+    P.host_lists_valid = false;
     P.d_thr.reserve(std::max(V, 1));
     P.d_bits.reserve(std::max<size_t>((size_t)W * Hl, 1));
     P.d_cnt.reserve(std::max(Hl, 1));
     P.d_off.reserve(Hl + 1);
-    SP_CUDA(cudaMemcpyAsync(P.d_thr.p, P.h_thr.data(), (size_t)V * 8, cudaMemcpyHostToDevice, st));
+    P.d_scalars.reserve(4);
+    if (!P.thr_uploaded) {
+        SP_CUDA(cudaMemcpyAsync(P.d_thr.p, P.h_thr.data(), (size_t)V * 8, cudaMemcpyHostToDevice, st));
+        P.thr_uploaded = true;
+    }
     const Affine stride = lcg_jump(2ull * (uint64_t)H);
     const int64_t nthreads = (int64_t)W * Hl;
     if (nthreads > 0) {
@@ -472,16 +493,21 @@ void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
         count_bits_kernel<<<Hl, 256, 0, st>>>(P.d_bits.p, W, P.d_cnt.p);
         c->launches += 2;
     }
-    scan_counts_kernel<<<1, 1024, 0, st>>>(P.d_cnt.p, Hl, P.d_off.p);
+    scan_counts_kernel<<<1, 1024, 0, st>>>(P.d_cnt.p, Hl, P.d_off.p, P.d_scalars.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());
-    std::vector<int64_t> off(Hl + 1);
-    SP_CUDA(cudaMemcpyAsync(off.data(), P.d_off.p, (Hl + 1) * 8, cudaMemcpyDeviceToHost, st));
-    SP_CUDA(cudaStreamSynchronize(st));
-    const int64_t total = off[Hl];
-    P.pre_total = total;
-    P.d_ids.reserve(std::max<int64_t>(total, 1));
-    P.d_fdeg.reserve(std::max<int64_t>(total, 1));
+    // The list buffers are sized by the bound V*Hl when that is small (a batch), so that the number of carriers does not
+    // have to come back to the host before the lists are expanded; a whole population takes the exact total first.
+    int64_t* hp = c->pinned((size_t)(Hl + 1) * 8 + 64);
+    int64_t total_cap = (int64_t)V * Hl;
+    const bool bounded = total_cap <= ((int64_t)1 << 24);
+    if (!bounded) {
+        SP_CUDA(cudaMemcpyAsync(hp, P.d_off.p + Hl, 8, cudaMemcpyDeviceToHost, st));
+        SP_CUDA(cudaStreamSynchronize(st));
+        total_cap = hp[0];
+    }
+    P.d_ids.reserve(std::max<int64_t>(total_cap, 1));
+    P.d_fdeg.reserve(std::max<int64_t>(total_cap, 1));
     P.d_nedges.reserve(std::max(Hl, 1));
     P.d_eoff.reserve(Hl + 1);
     if (Hl > 0) {
@@ -492,62 +518,62 @@ void run_genotype_and_collisions(sp_ctx* c, PopulationState& P) {
     scan_counts_kernel<<<1, 1024, 0, st>>>(P.d_nedges.p, Hl, P.d_eoff.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());
+    // one round trip: total carriers, longest list, total edges (+ the offsets when the raw matrix is kept for tests)
+    int32_t* hmax = (int32_t*)(hp + 2);
+    SP_CUDA(cudaMemcpyAsync(hp, P.d_off.p + Hl, 8, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(hp + 1, P.d_eoff.p + Hl, 8, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(hmax, P.d_scalars.p, 4, cudaMemcpyDeviceToHost, st));
     if (P.keep_pre_collision) {
-        P.h_pre_off = off;
+        P.h_pre_off.assign(Hl + 1, 0);
+        SP_CUDA(cudaMemcpyAsync(P.h_pre_off.data(), P.d_off.p, (size_t)(Hl + 1) * 8, cudaMemcpyDeviceToHost, st));
+    }
+    SP_CUDA(cudaStreamSynchronize(st));
+    const int64_t total = hp[0], etotal = hp[1];
+    const int32_t max_n = hmax[0];
+    P.pre_total = total;
+    if (P.keep_pre_collision) {
         P.h_pre_ids.assign((size_t)total, 0);
         if (total > 0) SP_CUDA(cudaMemcpyAsync(P.h_pre_ids.data(), P.d_ids.p, (size_t)total * 4, cudaMemcpyDeviceToHost, st));
     }
-    int64_t etotal = 0;
-    SP_CUDA(cudaMemcpyAsync(&etotal, P.d_eoff.p + Hl, 8, cudaMemcpyDeviceToHost, st));
-    SP_CUDA(cudaStreamSynchronize(st));
     P.d_adj.reserve(std::max<int64_t>(2 * etotal, 1));
-    P.d_adj_off.reserve(std::max<int64_t>(total + Hl + 1, 1));
-    P.d_q.reserve(std::max<int64_t>(total, 1));
-    P.d_where.reserve(std::max<int64_t>(total, 1));
-    P.d_degree.reserve(std::max<int64_t>(total, 1));
-    P.d_removed.reserve(std::max<int64_t>(total, 1));
     P.d_cnt2.reserve(std::max(Hl, 1));
     P.d_off2.reserve(Hl + 1);
     P.d_counts.reserve(std::max(V, 1));
-    P.d_nfixed.reserve(1);
-    SP_CUDA(cudaMemsetAsync(P.d_nfixed.p, 0, 4, st));
+    SP_CUDA(cudaMemsetAsync(P.d_scalars.p + 1, 0, 4, st));
+    int32_t* d_nfixed = P.d_scalars.p + 1;
     SP_CUDA(cudaMemsetAsync(P.d_counts.p, 0, (size_t)std::max(V, 1) * 4, st));
-    int32_t max_n = 0;
-    for (int32_t i = 0; i < Hl; i++) max_n = std::max<int32_t>(max_n, (int32_t)(off[i + 1] - off[i]));
     const size_t smem_bytes = (size_t)max_n * 38 + 64;
     const bool force_global = getenv("SYNTHPOP_FORCE_GLOBAL_COLLISION_FIX") != nullptr;  // test hook
     if (Hl > 0 && smem_bytes <= 200 * 1024 && !force_global) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            SP_CUDA(cudaFuncSetAttribute(collision_fix_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            attr_set = true;
-        }
+        // the attribute is per device and per context: set on every launch (cheap), not once per process
+        SP_CUDA(cudaFuncSetAttribute(collision_fix_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         collision_fix_smem_kernel<<<Hl, 32, smem_bytes, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, P.d_off.p, P.d_ids.p, P.d_fdeg.p,
-                                                              P.d_eoff.p, P.d_adj.p, max_n, P.d_cnt2.p, P.d_nfixed.p);
+                                                              P.d_eoff.p, P.d_adj.p, max_n, P.d_cnt2.p, d_nfixed);
         c->launches++;
     } else if (Hl > 0) {
+        P.d_adj_off.reserve(std::max<int64_t>(total + Hl + 1, 1));
+        P.d_q.reserve(std::max<int64_t>(total, 1));
+        P.d_where.reserve(std::max<int64_t>(total, 1));
+        P.d_degree.reserve(std::max<int64_t>(total, 1));
+        P.d_removed.reserve(std::max<int64_t>(total, 1));
         collision_fix_kernel<<<Hl, 32, 0, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, P.d_off.p, P.d_ids.p, P.d_fdeg.p, P.d_eoff.p,
                                                 P.d_adj.p, P.d_adj_off.p, P.d_q.p, P.d_where.p, P.d_degree.p, P.d_removed.p,
-                                                P.d_cnt2.p, P.d_nfixed.p);
+                                                P.d_cnt2.p, d_nfixed);
         c->launches++;
     }
     scan_counts_kernel<<<1, 1024, 0, st>>>(P.d_cnt2.p, Hl, P.d_off2.p);
     c->launches++;
-    P.d_ids2.reserve(std::max<int64_t>(total, 1));
+    P.d_ids2.reserve(std::max<int64_t>(bounded ? total_cap : total, 1));
     if (Hl > 0) {
         compact_count_kernel<<<Hl, 256, 0, st>>>(P.d_off.p, P.d_ids.p, P.d_cnt2.p, P.d_off2.p, P.d_ids2.p, P.d_counts.p);
         c->launches++;
     }
     SP_CUDA(cudaGetLastError());
-    P.h_off.assign(Hl + 1, 0);
-    SP_CUDA(cudaMemcpyAsync(P.h_off.data(), P.d_off2.p, (Hl + 1) * 8, cudaMemcpyDeviceToHost, st));
-    SP_CUDA(cudaMemcpyAsync(&P.n_haplotypes_with_collision, P.d_nfixed.p, 4, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(hp, P.d_off2.p, (size_t)(Hl + 1) * 8, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(hp + Hl + 1, d_nfixed, 4, cudaMemcpyDeviceToHost, st));
     SP_CUDA(cudaStreamSynchronize(st));
-    P.h_ids.assign((size_t)P.h_off[Hl], 0);
-    if (P.h_off[Hl] > 0) SP_CUDA(cudaMemcpyAsync(P.h_ids.data(), P.d_ids2.p, (size_t)P.h_off[Hl] * 4, cudaMemcpyDeviceToHost, st));
-    P.h_counts_local.assign(V, 0);
-    if (V > 0) SP_CUDA(cudaMemcpyAsync(P.h_counts_local.data(), P.d_counts.p, (size_t)V * 4, cudaMemcpyDeviceToHost, st));
-    SP_CUDA(cudaStreamSynchronize(st));
+    P.h_off.assign(hp, hp + Hl + 1);
+    P.n_haplotypes_with_collision = *(int32_t*)(hp + Hl + 1);
 }
 
 }  // namespace sp

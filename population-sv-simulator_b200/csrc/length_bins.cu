@@ -436,11 +436,6 @@ static int sample_bins(sp_ctx* c, const double* cdf, int32_t n_bins, int64_t tar
 
 using sp::Error;
 
-#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { cudaSetDevice(ctx->device);
-#define SP_API_END                                                                         \
-    return SP_OK; }                                                                        \
-    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
-    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }
 
 extern "C" {
 

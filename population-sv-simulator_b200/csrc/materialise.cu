@@ -406,6 +406,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
         throw Error(SP_ERR_JAVA_EXCEPTION, "ArrayIndexOutOfBoundsException: haplotype range [" + std::to_string(first) + ".." + std::to_string(last) + "]");
     const int nh = last - first + 1;
     c->materialised = false;
+    c->plan_last = -1; c->plan_first = 0;   // no valid plan while this one is being built
     // aux blob: "\n" at offset 0, then the FASTA headers ">chr1_<i>\n" (src/SimulateHaplotypes.java:955)
     std::vector<uint8_t> aux(1, (uint8_t)'\n');
     std::vector<int64_t> aux_off(nh + 1);
@@ -424,27 +425,33 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
     const int64_t l0 = lo_host[0];
     for (int i = 0; i <= nh; i++) seg_base[i] = 3 * (lo_host[i] - l0) + 5 * (int64_t)i;
     const int64_t nseg = seg_base[nh];
-    c->d_aux.reserve(aux.size());
-    c->d_aux_off.reserve(nh + 1);
-    c->d_seg_base.reserve(nh + 1);
-    c->d_seg_dst.reserve(nseg);
-    c->d_seg_src.reserve(nseg);
+    // The plan goes into the set the copy kernel in flight is not reading, on the planning stream when there is one: the
+    // round trip below then waits for the plan kernel alone, never for the copy kernel of the batch before.
+    cudaStream_t st = c->pop_stream ? c->pop_stream : c->stream;
+    const int ps = c->plan_cur ^ 1;
+    sp_ctx::PlanSet& B = c->plan_set[ps];
+    if (!B.ev_used) SP_CUDA(cudaEventCreateWithFlags(&B.ev_used, cudaEventDisableTiming));
+    else if (st != c->stream) SP_CUDA(cudaStreamWaitEvent(st, B.ev_used, 0));   // the copy kernel that last read this set
+    if (!c->ev_planned) SP_CUDA(cudaEventCreateWithFlags(&c->ev_planned, cudaEventDisableTiming));
+    B.aux.reserve(aux.size());
+    B.aux_off.reserve(nh + 1);
+    B.seg_base.reserve(nh + 1);
+    B.seg_dst.reserve(nseg);
+    B.seg_src.reserve(nseg);
     c->d_hap_len.reserve(nh);
     c->d_err.reserve(4);
-    cudaStream_t st = c->stream;
-    SP_CUDA(cudaMemcpyAsync(c->d_aux.p, aux.data(), aux.size(), cudaMemcpyHostToDevice, st));
-    SP_CUDA(cudaMemcpyAsync(c->d_aux_off.p, aux_off.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
-    SP_CUDA(cudaMemcpyAsync(c->d_seg_base.p, seg_base.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaMemcpyAsync(B.aux.p, aux.data(), aux.size(), cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaMemcpyAsync(B.aux_off.p, aux_off.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
+    SP_CUDA(cudaMemcpyAsync(B.seg_base.p, seg_base.data(), (nh + 1) * 8, cudaMemcpyHostToDevice, st));
     SP_CUDA(cudaMemsetAsync(c->d_err.p, 0, 16, st));
     plan_kernel<<<nh, 256, 0, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, c->d_payload_off.p, c->n_variants,
-                                    c->v_off_dev + (first - c->v_h0), c->v_ids_dev, c->ref_len, first, c->d_aux_off.p,
-                                    c->d_seg_base.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_hap_len.p, c->d_err.p);
+                                    c->v_off_dev + (first - c->v_h0), c->v_ids_dev, c->ref_len, first, B.aux_off.p,
+                                    B.seg_base.p, B.seg_dst.p, B.seg_src.p, c->d_hap_len.p, c->d_err.p);
     c->launches++;
     SP_CUDA(cudaGetLastError());
-    if (c->ev_plan) SP_CUDA(cudaEventRecord(c->ev_plan, st));
-    c->h_hap_len.assign(nh, 0);
-    int32_t err[4] = {0, 0, 0, 0};
-    SP_CUDA(cudaMemcpyAsync(c->h_hap_len.data(), c->d_hap_len.p, nh * 8, cudaMemcpyDeviceToHost, st));
+    int64_t* hp = c->pinned((size_t)nh * 8 + 16);
+    int32_t* err = (int32_t*)(hp + nh);
+    SP_CUDA(cudaMemcpyAsync(hp, c->d_hap_len.p, (size_t)nh * 8, cudaMemcpyDeviceToHost, st));
     SP_CUDA(cudaMemcpyAsync(err, c->d_err.p, 16, cudaMemcpyDeviceToHost, st));
     SP_CUDA(cudaStreamSynchronize(st));
     if (err[0] != 0) {
@@ -453,18 +460,21 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
         throw Error(err[0] == 4 ? SP_ERR_ARG : SP_ERR_JAVA_EXCEPTION,
                     std::string(what[err[0]]) + " (haplotype " + std::to_string(err[1]) + ", list index " + std::to_string(err[2]) + ")");
     }
+    c->h_hap_len.assign(hp, hp + nh);
     int64_t mx = 0;
     for (int i = 0; i < nh; i++) mx = std::max(mx, c->h_hap_len[i]);
     c->slot_stride = round_up(std::max<int64_t>(mx, 1), TILE_BYTES);
     c->tiles_per_slot = c->slot_stride / TILE_BYTES;
     const int64_t ntiles = c->tiles_per_slot * nh;
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "batch too large: reduce the haplotype range");
-    c->d_tile_desc.reserve(ntiles);
-    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(c->d_seg_dst.p, c->d_seg_src.p, c->d_seg_base.p, nh,
-                                                                        c->tiles_per_slot, c->d_tile_desc.p, 0);
+    B.tile_desc.reserve(ntiles);
+    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(B.seg_dst.p, B.seg_src.p, B.seg_base.p, nh,
+                                                                        c->tiles_per_slot, B.tile_desc.p, 0);
     c->launches++;
     SP_CUDA(cudaGetLastError());
+    SP_CUDA(cudaEventRecord(c->ev_planned, st));
     c->d_out.reserve((size_t)c->slot_stride * nh, 0.01);
+    c->plan_cur = ps;
     c->plan_first = first; c->plan_last = last; c->plan_framing = framing;
     if (out_lengths) for (int i = 0; i < nh; i++) out_lengths[i] = c->h_hap_len[i];
     if (slot_stride) *slot_stride = c->slot_stride;
@@ -474,10 +484,13 @@ void materialise(sp_ctx* c) {
     if (c->plan_last < c->plan_first) throw Error(SP_ERR_ARG, "sp_plan_haplotypes has not been called");
     const int nh = c->plan_last - c->plan_first + 1;
     const int64_t ntiles = c->tiles_per_slot * nh;
-    launch_materialise(c->stream, ntiles, c->d_ref.p, c->d_payload.p, c->d_aux.p, c->d_seg_dst.p, c->d_seg_src.p, c->d_seg_base.p,
-                       c->d_tile_desc.p, c->d_out.p, c->slot_stride, c->tiles_per_slot, nh, 0);
+    sp_ctx::PlanSet& B = c->plan_set[c->plan_cur];
+    SP_CUDA(cudaStreamWaitEvent(c->stream, c->ev_planned, 0));   // no-op when the plan ran on this stream
+    launch_materialise(c->stream, ntiles, c->d_ref.p, c->d_payload.p, B.aux.p, B.seg_dst.p, B.seg_src.p, B.seg_base.p,
+                       B.tile_desc.p, c->d_out.p, c->slot_stride, c->tiles_per_slot, nh, 0);
     c->launches++;
     SP_CUDA(cudaGetLastError());
+    SP_CUDA(cudaEventRecord(B.ev_used, c->stream));
     c->materialised = true;
 }
 

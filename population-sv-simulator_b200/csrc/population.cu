@@ -8,6 +8,12 @@
 namespace sp {
 
 void free_population(sp_ctx* c) {
+    if (!c->pop) return;
+    // the plan view may point at this state's device lists (sp_population_genotypes): fall back to the context's own
+    const bool viewing = c->v_off_dev == c->pop->d_off2.p || c->v_off_host == c->pop->h_off.data();
+    if (viewing) { c->view_own_lists(); c->plan_last = -1; c->plan_first = 0; }
+    if (c->pop_stream) cudaStreamSynchronize(c->pop_stream);
+    cudaStreamSynchronize(c->stream);
     delete c->pop;
     c->pop = nullptr;
 }
@@ -110,6 +116,7 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
     PopulationState& P = *c->pop;
     const int32_t V = P.n_variants, H = P.n_haplotypes_total, L = (int32_t)c->ref_len;
     const bool local_is_global = P.h0 == 0 && P.h1 == H;
+    fetch_host_lists(c, P);
     if (!global_counts && !local_is_global) throw Error(SP_ERR_ARG, "a sharded run needs the all-gathered carrier counts");
     P.counts_global.assign(V, 0);
     for (int32_t v = 0; v < V; v++) P.counts_global[v] = global_counts ? global_counts[v] : P.h_counts_local[v];
@@ -134,6 +141,8 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
     annotate_variants_with_repeats(P, 100);                             // :111
     const bool skip_individual = (write_joint & 2) != 0;
     write_joint &= 1;
+    if ((write_joint || !skip_individual) && (int64_t)c->h_ref.size() != c->ref_len)
+        throw Error(SP_ERR_ARG, "the VCF writers need the host copy of the reference this population was begun on");
     if (write_joint) {
         if (!P.have_all_lists) throw Error(SP_ERR_ARG, "the joint outputs need every haplotype's list");
         write_histograms(P, L);
@@ -184,6 +193,8 @@ void trio_add_child(sp_ctx* c, int32_t father, int32_t mother, int64_t seed, int
     }
     c->n_haplotypes = H + 2;
     upload_context_lists(c);
+    if (write_vcf && (int64_t)c->h_ref.size() != c->ref_len)
+        throw Error(SP_ERR_ARG, "the VCF writers need the host copy of the reference this population was begun on");
     if (write_vcf) write_individual_vcfs(P, c->h_ref.data(), (int32_t)c->ref_len, H, H + 1, c->h_list_off.data(), c->h_list_ids.data(), 0);
     if (child_first) *child_first = H;
     if (from_father) *from_father = hf;
@@ -207,11 +218,6 @@ void population_genotypes(sp_ctx* c, int32_t first, int32_t last) {
 
 using sp::Error;
 
-#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { cudaSetDevice(ctx->device);
-#define SP_API_END                                                                         \
-    return SP_OK; }                                                                        \
-    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
-    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }
 
 static sp::PopulationState& pop_of(sp_ctx* ctx) {
     if (!ctx->pop || !ctx->pop->begun) throw Error(SP_ERR_ARG, "sp_population_begin has not been called");
@@ -252,6 +258,7 @@ int sp_population_info(sp_ctx* ctx, int32_t* n_variants, int32_t* n_haplotypes, 
 int sp_population_local_counts(sp_ctx* ctx, int32_t* counts) {
     SP_API_BEGIN
     sp::PopulationState& P = pop_of(ctx);
+    sp::fetch_host_lists(ctx, P);
     if (P.n_variants > 0) memcpy(counts, P.h_counts_local.data(), (size_t)P.n_variants * 4);
     SP_API_END
 }
@@ -266,6 +273,7 @@ int sp_population_counts_device(sp_ctx* ctx, void** device_counts) {
 int sp_population_local_lists(sp_ctx* ctx, int64_t* off, int32_t* ids) {
     SP_API_BEGIN
     sp::PopulationState& P = pop_of(ctx);
+    sp::fetch_host_lists(ctx, P);
     if (off) memcpy(off, P.h_off.data(), P.h_off.size() * 8);
     if (ids && !P.h_ids.empty()) memcpy(ids, P.h_ids.data(), P.h_ids.size() * 4);
     SP_API_END

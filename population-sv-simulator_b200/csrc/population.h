@@ -42,7 +42,9 @@ struct PopulationState {
     std::vector<int64_t> h_thr;
     DevBuf<int64_t> d_thr, d_off, d_eoff, d_off2;
     DevBuf<uint32_t> d_bits;
-    DevBuf<int32_t> d_cnt, d_ids, d_fdeg, d_nedges, d_adj, d_adj_off, d_q, d_where, d_degree, d_cnt2, d_ids2, d_counts, d_nfixed;
+    DevBuf<int32_t> d_cnt, d_ids, d_fdeg, d_nedges, d_adj, d_adj_off, d_q, d_where, d_degree, d_cnt2, d_ids2, d_counts;
+    DevBuf<int32_t> d_scalars;            // [0] longest pre-collision list, [1] haplotypes the fixer changed
+    bool thr_uploaded = false;
     DevBuf<int8_t> d_removed;
     int64_t pre_total = 0;
     bool keep_pre_collision = false;
@@ -53,6 +55,7 @@ struct PopulationState {
     std::vector<int64_t> h_off;           // local CSR after collision fixing (h1-h0+1)
     std::vector<int32_t> h_ids;
     std::vector<int32_t> h_counts_local;  // carriers per variant among local haplotypes
+    bool host_lists_valid = false;        // h_ids / h_counts_local mirror the device (fetch_host_lists)
     int32_t n_haplotypes_with_collision = 0;
 
     // global view used by the writers (filled by finish(): from the local shard, or from all ranks)
@@ -64,6 +67,7 @@ struct PopulationState {
 };
 
 void run_genotype_and_collisions(sp_ctx* c, PopulationState& P);
+void fetch_host_lists(sp_ctx* c, PopulationState& P);
 void sample_variants(PopulationState& P, int64_t seed, int32_t reference_length);
 void assign_insertion_strings(PopulationState& P, int64_t seed);
 void annotate_variants_with_repeats(PopulationState& P, int maxDistance);

@@ -220,11 +220,6 @@ static void fetch_offsets(sp_ctx* c, ReadMixState& M) {
 
 using sp::Error;
 
-#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { cudaSetDevice(ctx->device);
-#define SP_API_END                                                                         \
-    return SP_OK; }                                                                        \
-    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
-    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }
 
 extern "C" {
 
@@ -301,16 +296,28 @@ int sp_reads_mix_timing(sp_ctx* ctx, double* order_ms, double* copy_ms) {
     SP_API_END
 }
 
+uint32_t sp_haplotype_read_seed(uint32_t seed, int32_t haplotype) {
+    uint64_t z = (uint64_t)seed * 0x9E3779B97F4A7C15ULL + ((uint64_t)(uint32_t)haplotype + 1) * 0xD6E8FEB86659FD93ULL;
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ULL;
+    z ^= z >> 27; z *= 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    return (uint32_t)(1 + z % 2147483646ULL);
+}
+
 // docker/haplotype2reads.sh:53-64 for the individual whose haplotypes are id1 and id1+1: pbsim on both haplotypes
-// (each its own process in the reference, hence ref_num 1 and the same seed for both), cat, shuf, tr, one file.
+// (each its own process in the reference, hence ref_num 1 and an independent seed for each), cat, shuf, tr, one file.
 int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const char* output_file, int64_t* n_reads,
                        int64_t* file_bytes) {
     SP_API_BEGIN
     int rc = sp_plan_haplotypes(ctx, id1, id1 + 1, 0, nullptr, nullptr);
     if (rc == SP_OK) rc = sp_materialise(ctx);
     if (rc == SP_OK) rc = sp_reads_mix_begin(ctx);
+    if (rc == SP_OK && (!ctx->reads || !ctx->reads->configured)) throw Error(SP_ERR_ARG, "sp_reads_configure has not been called");
+    const uint32_t seed0 = rc == SP_OK ? ctx->reads->par.seed : 0;
     for (int h = id1; h <= id1 + 1 && rc == SP_OK; h++) {
+        ctx->reads->par.seed = sp_haplotype_read_seed(seed0, h);
         rc = sp_reads_simulate_haplotype(ctx, h, 1, nullptr, nullptr, nullptr, nullptr);
+        ctx->reads->par.seed = seed0;
         if (rc == SP_OK) rc = sp_reads_mix_add(ctx);
     }
     if (rc == SP_OK) rc = sp_reads_mix_finish(ctx, shuffle_seed, n_reads, file_bytes);

@@ -737,12 +737,8 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     {   // Shared memory against L1: the generator state columns are 17 KB per CTA, but the table walks, the template
         // chunks and the scratch words live in L1. Measured at 30x chr1: the driver's default split (5 CTAs per SM, large
         // L1) 88 ms, the largest carve-out (8 CTAs per SM) 119 ms. SYNTHPOP_READS_CARVEOUT (percent) is a tuning hook.
-        static bool carveout_set = false;
-        if (!carveout_set) {
-            if (const char* e = getenv("SYNTHPOP_READS_CARVEOUT"))
-                SP_CUDA(cudaFuncSetAttribute(reads_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
-            carveout_set = true;
-        }
+        if (const char* e = getenv("SYNTHPOP_READS_CARVEOUT"))   // the attribute is per device: set on every launch (cheap)
+            SP_CUDA(cudaFuncSetAttribute(reads_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
     }
     if (replay) SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<true>, RD_THREADS, 0));
     else SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<false>, RD_THREADS, 0));
@@ -856,11 +852,6 @@ static void read_fasta_sequences(const char* path, std::vector<std::vector<uint8
 
 using sp::Error;
 
-#define SP_API_BEGIN if (!ctx) return SP_ERR_ARG; try { cudaSetDevice(ctx->device);
-#define SP_API_END                                                                         \
-    return SP_OK; }                                                                        \
-    catch (const sp::Error& e) { ctx->err = e.what(); return e.code; }                     \
-    catch (const std::exception& e) { ctx->err = e.what(); return SP_ERR; }
 
 static void report(sp::ReadState& R, int64_t* n_reads, int64_t* file_bytes, int64_t* n_dropped, int64_t* bases) {
     if (n_reads) *n_reads = R.n_reads;

@@ -28,7 +28,7 @@ int main(int argc, char** argv) {
         else break;
     }
     if (a >= argc) {
-        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|pbsim|haplotype2reads> <argv of the reference's command>\n");
+        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|pbsim|haplotype2reads> <argv of the reference's command>\n");
         return 2;
     }
     const std::string cls = argv[a++];
@@ -117,6 +117,13 @@ int main(int argc, char** argv) {
             sp_destroy(ctx);
             return 255;
         }
+    } else if (cls == "AnnotateVCF") {
+        // INPUT_FILES_LIST MIN_DISTANCE MAX_DISTANCE REFERENCE_FILE REPEAT_INTERVALS_FILE SEGDUPS_FILE (src/AnnotateVCF.java:96-102)
+        if (args.size() < 6) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
+        sp_annotate_args aa;
+        aa.input_files_list = args[0]; aa.min_distance = atoi(args[1]); aa.max_distance = atoi(args[2]);
+        aa.reference_file = args[3]; aa.repeat_intervals_file = args[4]; aa.segdups_file = args[5];
+        rc = sp_annotate_vcf(ctx, &aa);
     } else if (cls == "haplotype2reads") {
         // docker/haplotype2reads.sh:16-24,31-32,53-64 for one individual, without the haplotype_<i>.fa files and the bucket:
         // ID1 LENGTH_MIN LENGTH_MAX LENGTH_MEAN LENGTH_STDEV MAX_COVERAGE REFERENCE_FILE HAPLOTYPE2VARIANTS_FILE VARIANTS_FILE

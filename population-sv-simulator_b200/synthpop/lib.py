@@ -124,6 +124,7 @@ def load() -> C.CDLL:
         "sp_reads_mix_offsets": (C.c_int, [vp, vp]),
         "sp_reads_mix_timing": (C.c_int, [vp, vp, vp]),
         "sp_haplotype2reads": (C.c_int, [vp, i32, i64, cp, vp, vp]),
+        "sp_haplotype_read_seed": (C.c_uint32, [C.c_uint32, i32]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
         "sp_reference_length": (i64, [vp]),
@@ -165,6 +166,10 @@ def load() -> C.CDLL:
         "sp_length_bins_sample": (C.c_int, [vp, vp, i32, i64, P(i64), P(i64), P(i64), P(i64), vp]),
         "sp_length_bins_copy": (C.c_int, [vp, vp, i64, P(i64)]),
         "sp_length_bins_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double)]),
+        "sp_annotate_vcf": (C.c_int, [vp, P(AnnotateArgs)]),
+        "sp_annotate_load": (C.c_int, [vp, cp, cp, cp]),
+        "sp_annotate_file": (C.c_int, [vp, cp, cp, i32, i32, P(i64)]),
+        "sp_annotate_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double), P(i64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -174,6 +179,11 @@ def load() -> C.CDLL:
     lib._declared = set(sig)
     _lib = lib
     return lib
+
+
+def haplotype_read_seed(seed: int, haplotype: int) -> int:
+    """The pbsim seed sp_haplotype2reads derives for one haplotype (the reference runs one time(NULL)-seeded process each)."""
+    return int(load().sp_haplotype_read_seed(seed, haplotype))
 
 
 def declared_symbols() -> list[str]:
@@ -516,6 +526,29 @@ class Context:
         w = C.c_int64()
         self._check(self.lib.sp_length_bins_copy(self.h, _ptr(out), out.size, C.byref(w)))
         return out[:w.value]
+
+    # ---- §8(f) rank 2: AnnotateVCF ---------------------------------------------------------------------------------------
+    def annotate_vcf(self, argv):
+        """AnnotateVCF.main(args) (src/AnnotateVCF.java:96-124): INPUT_FILES_LIST MIN_DISTANCE MAX_DISTANCE REFERENCE_FILE
+        REPEAT_INTERVALS_FILE SEGDUPS_FILE; writes <input up to .vcf>_annotated.vcf beside every listed file."""
+        a = [str(x) for x in argv]
+        if len(a) < 6:
+            raise IndexError("AnnotateVCF takes 6 positional arguments")
+        args = AnnotateArgs(a[0].encode(), int(a[1]), int(a[2]), a[3].encode(), a[4].encode(), a[5].encode())
+        self._check(self.lib.sp_annotate_vcf(self.h, C.byref(args)))
+
+    def annotate_load(self, reference_file: str, repeat_intervals_file: str, segdups_file: str):
+        self._check(self.lib.sp_annotate_load(self.h, reference_file.encode(), repeat_intervals_file.encode(), segdups_file.encode()))
+
+    def annotate_file(self, input_vcf: str, output_vcf: str, min_distance: int, max_distance: int) -> int:
+        n = C.c_int64()
+        self._check(self.lib.sp_annotate_file(self.h, input_vcf.encode(), output_vcf.encode(), min_distance, max_distance, C.byref(n)))
+        return n.value
+
+    def annotate_timing(self):
+        a, b, n = C.c_double(), C.c_double(), C.c_int64()
+        self._check(self.lib.sp_annotate_timing(self.h, C.byref(a), C.byref(b), C.byref(n)))
+        return dict(load_s=a.value, kernel_ms=b.value, records=n.value)
 
     def length_bins_timing(self):
         a, b = C.c_double(), C.c_double()

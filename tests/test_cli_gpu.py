@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 CLI = os.path.join(ROOT, "population-sv-simulator_b200", "synthpop_cli")
 
 
-def test_print_haplotypes_and_haplotype2reads_commands(oracle_bin, oracle_lib, tmp_path):
+def test_print_haplotypes_and_haplotype2reads_commands(sp, oracle_bin, oracle_lib, tmp_path):
     from synthpop import synth
     assert os.path.exists(CLI), "synthpop_cli is missing: run __graft_entry__.build()"
     inp = synth.generate_population_inputs(str(tmp_path / "in"), 1_200_000, n_insertions=1500, seed=8)
@@ -41,7 +41,7 @@ def test_print_haplotypes_and_haplotype2reads_commands(oracle_bin, oracle_lib, t
     recs = []
     for h in (2, 3):
         hap = np.frombuffer(open(f"{hw}/haplotype_{h}.fa", "rb").read().split(b"\n")[1], np.uint8)
-        w, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=11, per_read_streams=True, ref_num=1, **p)
+        w, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=sp.haplotype_read_seed(11, h), per_read_streams=True, ref_num=1, **p)
         recs.append(w.tobytes())
     assert open(out, "rb").read() == rm.mix_reads(recs, 11)
 

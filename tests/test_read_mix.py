@@ -119,6 +119,8 @@ def test_haplotype2reads_whole_script(sp, oracle_lib, tmp_path):
     for h in range(2):
         hap = oh.build_haplotype(oracle_lib, case["ref"], case["sv_type"], case["position"], case["length"],
                                  case["payload_off"], case["payload"], None, case["lists"][h])
-        want, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=1, **p)
+        # one pbsim process per haplotype in the reference, each with its own seed (docker/haplotype2reads.sh:53-58)
+        want, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=sp.haplotype_read_seed(21, h), per_read_streams=True, ref_num=1, **p)
         files.append(want.tobytes())
     assert open(out, "rb").read() == rm.mix_reads(files, 77)
+    assert files[0][:4000] != files[1][:4000] and sp.haplotype_read_seed(21, 0) != sp.haplotype_read_seed(21, 1)

@@ -76,10 +76,13 @@ def test_child_haplotypes_vcf_and_coverage_sweep(sp, oracle_bin, oracle_lib, tmp
         n, nbytes = ctx.haplotype2reads(12, 9)
         mixed = ctx.reads_mix_copy(0, nbytes).tobytes()
         files = []
-        for parent in (3, 8):
+        for ch, parent in ((12, 3), (13, 8)):
             hap = np.frombuffer(open(f"{hw}/haplotype_{parent}.fa", "rb").read().split(b"\n")[1], np.uint8)
-            w, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=1, **p)
+            # the child's haplotype is sequenced in its own pbsim run: its reads are NOT the parent's reads
+            w, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=sp.haplotype_read_seed(21, ch), per_read_streams=True, ref_num=1, **p)
             files.append(w.tobytes())
+            wp, _ = oh.pbsim_simulate(oracle_lib, hap, model, seed=sp.haplotype_read_seed(21, parent), per_read_streams=True, ref_num=1, **p)
+            assert wp.tobytes() != files[-1]
         assert mixed == rm.mix_reads(files, 9)
         sizes = [ctx.reads_mix_coverage_prefix(3, c)["bytes"] for c in (1, 2, 3)]
         assert sizes == [len(rm.coverage_prefix(mixed, 3, c)) for c in (1, 2, 3)] and sizes[0] < sizes[1] < sizes[2] <= nbytes
