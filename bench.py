@@ -40,15 +40,17 @@ def measured_peak_gbs():
     return 6650.0, "fallback"
 
 
-def measured_traffic(batch: int, L: int):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one materialise_kernel launch, from the committed `ncu --set full`
-    capture (profiles/r01_traffic.json); only quoted when this run's launch has the captured shape."""
-    p = os.path.join(ROOT, "profiles", "r01_traffic.json")
+def measured_traffic(batch: int, L: int, bases_per_launch: float):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one materialise_kernel launch of THIS step shape, from the committed ncu
+    capture of `bench.py` itself (profiles/r02_traffic.json, made by tools/capture_traffic.py). A capture whose launch shape
+    differs (batch, reference length, or bases per launch off by more than 1 %) is not quoted: returns None."""
+    p = os.path.join(ROOT, "profiles", "r02_traffic.json")
     if os.path.exists(p):
         t = json.load(open(p))
-        if t.get("batch") == batch and t.get("reference_length") == L:
-            return t["dram_bytes_per_launch"]
-    return None
+        if (t.get("batch") == batch and t.get("reference_length") == L and
+                abs(t.get("bases_per_launch", 0) - bases_per_launch) <= 0.01 * bases_per_launch):
+            return float(t["dram_bytes_per_launch"]), t
+    return None, None
 
 
 def synth_population(L: int, H: int, seed: int = 20261104):
@@ -338,6 +340,133 @@ def _ref_arm_one(h):
     return int(out.size)
 
 
+def workload_config(L: int, batch: int, n_variants: int, entries: int):
+    """The `config` object: identical in both arms (the population is the same SimulateHaplotypes run: same generator seed for
+    the inputs, same java.util.Random seed)."""
+    return {"workload": f"chr1-sized reference ({L} bp), {N_HAPLOTYPES} haplotypes, genotype sampling + materialisation in batches of {batch}",
+            "population": "SimulateHaplotypes (seed 42) on the seeded synthetic GRCh38-chr1-shaped inputs of synthpop.synth "
+                          "(generator seed 20261104): AF threshold 0.01, 5000 frequent variants, 500 individuals",
+            "n_variants": int(n_variants), "variants_per_haplotype": round(entries / N_HAPLOTYPES, 1),
+            "l2": "inputs larger than L2 (>=31 GB written per step of 125 haplotypes, 249 MB per haplotype)"}
+
+
+def parse_population_files(out_dir: str):
+    """variants.txt + haplotype2variants.txt (src/SimulateHaplotypes.java:1123-1144) -> arrays for buildHaplotypes."""
+    with open(os.path.join(out_dir, "variants.txt")) as f:
+        rows = f.read().split("\n")
+    n = int(rows[0]) + 1
+    sv_type = np.zeros(n, np.int8); position = np.zeros(n, np.int32); length = np.zeros(n, np.int32)
+    payload_off = np.zeros(n + 1, np.int64)
+    chunks = []
+    for i in range(n):
+        r = rows[1 + 10 * i: 11 + 10 * i]
+        sv_type[i] = int(r[0]); length[i] = int(r[2]); position[i] = int(r[4])
+        seq = r[6]
+        if seq != "null":
+            chunks.append(seq.encode())
+            payload_off[i + 1] = payload_off[i] + len(seq)
+        else:
+            payload_off[i + 1] = payload_off[i]
+    payload = np.frombuffer(b"".join(chunks), np.uint8).copy() if chunks else np.zeros(1, np.uint8)
+    lists = []
+    with open(os.path.join(out_dir, "haplotype2variants.txt")) as f:
+        H = int(f.readline())
+        for _ in range(H):
+            t = f.readline().rstrip("\n").split(",")
+            lists.append(np.array([int(x) for x in t[1:2 + int(t[0])]], np.int32))
+    return dict(sv_type=sv_type, position=position, length=length, payload_off=payload_off, payload=payload, lists=lists)
+
+
+def reference_arm(args, L):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores. No JVM exists in this image,
+    so it is the C++ restatement (oracle/, kind "port"): SimulateHaplotypes once (single process, as the reference runs
+    it) on the SAME inputs and seed as the b200 arm, then buildHaplotypes in one process per core (the WDL scatters one
+    JVM per individual, wdl/SimulateHaplotypes.wdl:263). A step = `cores` haplotypes; the genotype sampling + collision
+    fixing the reference does for all 1 000 haplotypes in one sequential pass is charged per haplotype."""
+    import multiprocessing as mp
+    import tempfile
+    import shutil
+    from synthpop import synth
+    import oracle_helpers as oh
+    oh.ensure_oracle_built()
+    cores = len(os.sched_getaffinity(0))
+    work = tempfile.mkdtemp(prefix="synthpop_ref_arm_")
+    inp = synth.generate_population_inputs(os.path.join(work, "in"), L, n_insertions=30000)
+    out_dir = os.path.join(work, "out"); os.makedirs(out_dir)
+    log = os.path.join(work, "draw.log")
+    t0 = time.perf_counter()
+    subprocess.run([os.path.join(ROOT, "oracle", "_build", "synthpop_oracle"), "--seed", "42", "--quiet", "--draw-log", log,
+                    "SimulateHaplotypes"] + inp.simulate_argv(out_dir, N_HAPLOTYPES // 2, n_frequent=5000), check=True)
+    t_sim = time.perf_counter() - t0
+    phases = {k[len("seconds_"):]: float(v) for k, v in (l.split("=") for l in open(log).read().split()) if k.startswith("seconds_")}
+    t_pop_per_hap = phases.get("buildPopulation", 0.0) / N_HAPLOTYPES
+    pop = parse_population_files(out_dir)
+    ref = inp.extra["bases"]
+    entries = sum(l.size for l in pop["lists"])
+    global _REF_ARM
+    _REF_ARM = (ref, pop)
+    vals, t_all = [], []
+    with mp.get_context("fork").Pool(cores) as pool:
+        h = 0
+        for s in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            bases = sum(pool.map(_ref_arm_one, [(h + k) % N_HAPLOTYPES for k in range(cores)], chunksize=1))
+            h += cores
+            dt = time.perf_counter() - t0 + cores * t_pop_per_hap
+            if s >= args.warmup:
+                vals.append(bases / dt / 1e9)
+                t_all.append(dt)
+    v = float(np.mean(vals))
+    line = {"metric": "simulated haplotype Gbp/s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(t_all)), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
+            "config": workload_config(L, args.batch, pop["sv_type"].size, entries),
+            "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": cores, "kind": "port",
+                             "sample": f"{cores} chr1-sized haplotypes per step, one buildHaplotypes process per host core, plus "
+                                       f"{1e3 * t_pop_per_hap:.2f} ms per haplotype of the single-threaded buildPopulation "
+                                       f"(CPU restatement; the reference is Java and no JVM exists in this image)"},
+            "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "prologue_s": {"total_SimulateHaplotypes": round(t_sim, 2), **{k: round(x, 3) for k, x in phases.items()}}}
+    print(json.dumps(line))
+    shutil.rmtree(work, ignore_errors=True)
+
+
+def pcie_d2h_peak(torch, nbytes=1 << 30):
+    """Measured device-to-host copy rate of this box into pinned memory (the bound of the end-to-end leg)."""
+    d = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    h = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    best = 0.0
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); h.copy_(d, non_blocking=True); e1.record(); torch.cuda.synchronize()
+        best = max(best, nbytes / (e0.elapsed_time(e1) / 1e3) / 1e9)
+    return best
+
+
+def file_emission_leg(splib, synth, work, local_rank):
+    """BASELINE configs[0] (chr21-sized reference, 10 individuals) THROUGH THE FILES: SimulateHaplotypes with its six outputs
+    and PrintHaplotypes of all 20 haplotypes (src/SimulateHaplotypes.java:113-115, src/PrintHaplotypes.java:6-18)."""
+    Lc = 46_709_983
+    t0 = time.perf_counter()
+    inp = synth.generate_population_inputs(os.path.join(work, "c1_in"), Lc, n_insertions=30000)
+    t_gen = time.perf_counter() - t0
+    out = os.path.join(work, "c1_out"); os.makedirs(out)
+    with splib.Context(local_rank, 42) as ctx:
+        t0 = time.perf_counter()
+        ctx.simulate_haplotypes(inp.simulate_argv(out, 10, n_frequent=5000))
+        t_sim = time.perf_counter() - t0
+        rows = ctx.population_timing()
+        vcf_bytes = sum(os.path.getsize(os.path.join(out, f)) for f in os.listdir(out) if f.endswith(".vcf"))
+        t0 = time.perf_counter()
+        ctx.print_haplotypes(0, 19, inp.reference_file, os.path.join(out, "haplotype2variants.txt"), os.path.join(out, "variants.txt"), out)
+        t_print = time.perf_counter() - t0
+    fa_bytes = sum(os.path.getsize(os.path.join(out, f)) for f in os.listdir(out) if f.endswith(".fa"))
+    return {"workload": "configs[0]: chr21-sized reference (46709983 bp), 10 individuals, files on local disk",
+            "generate_inputs_s": round(t_gen, 2), "simulate_haplotypes_s": round(t_sim, 3), "rows_s": {k: round(v, 4) for k, v in rows.items()},
+            "vcf_bytes": vcf_bytes, "vcf_MBps": vcf_bytes / max(rows["W_buildVCF"], 1e-9) / 1e6,
+            "print_haplotypes_s": round(t_print, 3), "fasta_bytes": fa_bytes, "print_haplotypes_MBps": fa_bytes / t_print / 1e6}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -348,10 +477,11 @@ def main():
     ap.add_argument("--length", type=int, default=CHR1)
     ap.add_argument("--e2e-haplotypes", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-overlap", action="store_true", help="genotype/collision kernels on the materialisation stream")
+    ap.add_argument("--no-overlap", action="store_true", help="genotype/collision/plan kernels on the materialisation stream")
     ap.add_argument("--read-haplotypes", type=int, default=2, help="haplotypes of the CCS read leg (0 = skip)")
     ap.add_argument("--read-depth", type=int, default=30)
     ap.add_argument("--length-bins", type=int, default=1, help="row D leg (SampleReadsFromLengthBins), 0 = skip")
+    ap.add_argument("--file-emission", type=int, default=1, help="configs[0] through the files (rank 0, N=1), 0 = skip")
     ap.add_argument("--read-quality", default="phred", choices=["phred", "high"], help="emission centres of the synthetic HMM quality model")
     args = ap.parse_args()
 
@@ -359,45 +489,15 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     L = args.length
-    workload = f"chr1-sized reference ({L} bp), {N_HAPLOTYPES} haplotypes, genotype sampling + materialisation in batches of {args.batch}"
 
     if args.impl == "reference":
-        if rank != 0:
-            return
-        # The reference path is single-threaded by construction (one JVM per individual, wdl/SimulateHaplotypes.wdl:263);
-        # "all the host threads it can use" = one process per core, each building whole haplotypes, as the WDL scatter does.
-        import multiprocessing as mp
-        cores = len(os.sched_getaffinity(0))
-        ref = random_reference(L)
-        pop = synth_population(L, max(64, cores))
-        global _REF_ARM
-        _REF_ARM = (ref, pop)
-        vals, t_all = [], []
-        with mp.get_context("fork").Pool(cores) as pool:
-            h = 0
-            for s in range(args.warmup + args.steps):
-                t0 = time.perf_counter()
-                bases = sum(pool.map(_ref_arm_one, [(h + k) % len(pop["lists"]) for k in range(cores)], chunksize=1))
-                h += cores
-                dt = time.perf_counter() - t0
-                if s >= args.warmup:
-                    vals.append(bases / dt / 1e9)
-                    t_all.append(dt)
-        v = float(np.mean(vals))
-        line = {"metric": "simulated haplotype Gbp/s", "value": v, "unit": "Gbp/s", "n_gpus": args.gpus, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(t_all)), "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
-                "config": {"workload": workload, "l2": "inputs larger than L2"},
-                "cpu_baseline": {"value": v, "unit": "Gbp/s", "cores": cores, "kind": "port",
-                                 "sample": f"{cores} chr1-sized haplotypes per step, one process per host core (CPU restatement of "
-                                           f"buildHaplotypes; the reference is Java and no JVM exists in this image)"},
-                "e2e": {"value": v, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        if rank == 0:
+            reference_arm(args, L)
         return
 
     import tempfile
     import torch
-    from synthpop import lib as splib, synth
+    from synthpop import lib as splib, synth, sharded
 
     torch.cuda.set_device(local_rank)
     dist = None
@@ -405,35 +505,65 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    # synthetic GRCh38-chr1-shaped inputs in the reference's own file formats (seeded; every rank makes the same)
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # synthetic GRCh38-chr1-shaped inputs in the reference's own file formats (seeded). One rank of the box writes them,
+    # every rank reads them: the files are identical by construction and the host cores are shared.
+    shared = os.path.join(tempfile.gettempdir(), f"synthpop_bench_{os.environ.get('MASTER_PORT', 'solo')}_{os.getppid() if world > 1 else os.getpid()}")
     work = tempfile.mkdtemp(prefix=f"synthpop_bench_r{rank}_")
     t_gen = time.perf_counter()
-    inp = synth.generate_population_inputs(os.path.join(work, "in"), L, n_insertions=30000)
+    if local_rank == 0:
+        inp = synth.generate_population_inputs(os.path.join(shared, "in"), L, n_insertions=30000)
+    barrier()
+    if local_rank != 0:
+        inp = synth.generate_population_inputs(os.path.join(shared, "in"), L, n_insertions=30000, reuse=True)
     t_gen = time.perf_counter() - t_gen
     out_dir = os.path.join(work, "out"); os.makedirs(out_dir)
     argv = inp.simulate_argv(out_dir, N_HAPLOTYPES // 2, n_frequent=5000)
     ctx = splib.Context(local_rank, 42)
     stream = torch.cuda.Stream()
     ctx.set_stream(stream.cuda_stream)
-    pop_stream = torch.cuda.Stream(priority=-1)   # high priority, or its CTAs queue behind the 1.8 M tiles; rows G/C/N of batch s+1 run under the materialisation kernel of batch s
-    # SimulateHaplotypes once, untimed: loaders, variant sampling, genotype matrix + collision fixer over all 1 000
-    # haplotypes, insertion strings, repeat annotation (no file emission)
+    pop_stream = torch.cuda.Stream(priority=-1)   # high priority, or its CTAs queue behind the 1.8 M tiles of the copy kernel
+
+    # ---- (1) SimulateHaplotypes sharded by individual over the ranks, with the path's ONE exchange (all-gather of the
+    # carrier counts, then of the lists for the joint outputs), checked against the same run done by this rank alone
+    collective = None
+    if dist is not None:
+        t0 = time.perf_counter()
+        res = sharded.simulate_population_sharded(ctx, argv, dist, write_files=False)
+        t_sharded = time.perf_counter() - t0
+        collective = dict(res["collective"], sharded_simulate_s=round(t_sharded, 3), shard=[int(res["first"]), int(res["last"])])
+    # SimulateHaplotypes over all 1 000 haplotypes on this rank alone, untimed: loaders, variant sampling, genotype matrix +
+    # collision fixer, insertion strings, repeat annotation (no file emission)
     t_pop = time.perf_counter()
     ctx.population_begin(argv, 0, -1)
     ctx.population_finish(None, None, None, 2)
     t_pop = time.perf_counter() - t_pop
+    prologue_rows = ctx.population_timing()
     info = ctx.population_info()
+    if dist is not None:
+        counts_alone = ctx.population_local_counts()
+        off_alone, ids_alone = ctx.get_haplotype_lists()
+        ok = (np.array_equal(res["counts"], counts_alone) and np.array_equal(res["all_off"], off_alone) and
+              np.array_equal(res["all_ids"], ids_alone))
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        collective["check"] = "ok" if int(flag[0]) == 1 else "MISMATCH"
+        collective["what"] = ("ncclAllGather of int32 carrier counts [V] per rank (summed -> AF, isActive), then of the CSR lists; "
+                              "global counts and every haplotype list equal the single-rank run of the same seed")
+        if collective["check"] != "ok":
+            print(json.dumps({"error": "sharded SimulateHaplotypes differs from the single-rank run", "collective": collective}))
+            sys.exit(1)
 
-    # each rank owns its own batches of haplotypes (weak scaling: `batch` haplotypes per step per GPU)
+    # ---- (2) the timed region: each rank owns its own batches of haplotypes (weak scaling: `batch` haplotypes per step per GPU)
     nb = N_HAPLOTYPES // args.batch
+
     def batch_range(step):
         b = (step + rank * 3) % nb
         return b * args.batch, b * args.batch + args.batch - 1
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     launches0 = 0
     step_events = []
@@ -441,7 +571,8 @@ def main():
     sampler = ClockSampler(local_rank)
     ctx.set_population_stream(None if args.no_overlap else pop_stream.cuda_stream)
     ev_region = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    t_geno = 0.0
+    t_geno = t_plan_host = 0.0
+    last = None
     for s in range(args.warmup + args.steps):
         if s == args.warmup:
             barrier()
@@ -451,41 +582,64 @@ def main():
             ev_region[0].record(stream)
         a, b = batch_range(s)
         with torch.cuda.stream(stream):
-            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
             tg = time.perf_counter()
             ctx.population_genotypes(a, b)            # rows G/C/N: genotype sampling for this batch (returns complete)
-            tg = time.perf_counter() - tg
+            tp = time.perf_counter()
+            lens, stride = ctx.plan_haplotypes(a, b, False)   # row M: segment scan + tile table (planning stream)
+            tq = time.perf_counter()
             ev[0].record(stream)
-            lens, stride = ctx.plan_haplotypes(a, b, False)   # row M: segment scan + tile table
-            ev[1].record(stream)
             ctx.materialise()                          # row M: tiled copy kernel
-            ev[2].record(stream)
+            ev[1].record(stream)
         if s >= args.warmup:
             step_events.append(ev)
             bases_total += int(lens.sum())
-            t_geno += tg
+            t_geno += tp - tg
+            t_plan_host += tq - tp
+        last = (a, b, lens, stride)
     ev_region[1].record(stream)
     barrier()
     t_wall = time.perf_counter() - t_wall0
     sampler.stop_flag = True
-    ctx.set_population_stream(None)
     launches = ctx.kernel_launches - launches0
     # the timed region: first event before step W's genotype call, last after step W+K-1's materialisation kernel
     t_step = ev_region[0].elapsed_time(ev_region[1]) / 1e3
-    t_plan = sum(e[0].elapsed_time(e[1]) for e in step_events) / 1e3
-    t_kernel = sum(e[1].elapsed_time(e[2]) for e in step_events) / 1e3
-    t = torch.tensor([t_step, t_kernel, float(bases_total)], dtype=torch.float64, device="cuda")
+    t_kernel = sum(e[0].elapsed_time(e[1]) for e in step_events) / 1e3
+    mine = torch.tensor([t_step, t_kernel, float(bases_total), t_geno, t_plan_host], dtype=torch.float64, device="cuda")
     if dist is not None:
-        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        t_step_max, t_kernel_max, bases_all = float(tmax[0]), float(tmax[1]), float(tsum[2])
+        allr = torch.empty(world * mine.numel(), dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(allr, mine)
+        allr = allr.view(world, -1).cpu().numpy()
     else:
-        t_step_max, t_kernel_max, bases_all = t_step, t_kernel, float(bases_total)
+        allr = mine.view(1, -1).cpu().numpy()
+    t_step_max, t_kernel_max, bases_all = float(allr[:, 0].max()), float(allr[:, 1].max()), float(allr[:, 2].sum())
     value = bases_all / t_step_max / 1e9
+
+    # ---- (3) parity spot check on the LAST timed batch: one haplotype back to the host, against the CPU restatement of
+    # buildHaplotypes on the sampler's own lists (the batch's lists are still on the device)
+    import oracle_helpers as oh
+    a, b, lens, stride = last
+    ctx.synchronize()
     pop = ctx.get_variants()
+    off_b, ids_b = ctx.population_local_lists(b - a + 1)
+    hsel = a + (rank * 7 + 3) % (b - a + 1)
+    lst = ids_b[off_b[hsel - a]:off_b[hsel - a + 1]]
+    got = ctx.copy_haplotype(hsel, stride)
+    ref = inp.extra["bases"]
+    want = oh.build_haplotype(oh.load_oracle(), ref, pop["sv_type"], pop["position"], pop["length"], pop["payload_off"],
+                              pop["payload"], None, lst)
+    spot_ok = got.size == want.size and np.array_equal(got, want)
+    flag = torch.tensor([1 if spot_ok else 0], dtype=torch.int32, device="cuda")
+    if dist is not None:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag[0]) != 1:
+        if rank == 0:
+            print(json.dumps({"error": "parity spot check failed: a haplotype of the last timed batch differs from the CPU restatement",
+                              "haplotype": int(hsel), "rank_local_ok": bool(spot_ok)}))
+        sys.exit(1)
+    ctx.set_population_stream(None)
     pop["list_off"], pop["ids"] = ctx.get_haplotype_lists()
     pop["lists"] = [pop["ids"][pop["list_off"][h]:pop["list_off"][h + 1]] for h in range(64)]
-    ref = inp.extra["bases"]
 
     # CCS read leg (row P): every rank simulates reads over its own haplotypes; no collective
     reads_obj = None
@@ -509,6 +663,7 @@ def main():
 
     # e2e: the reference-facing call with HOST buffers — reference + variant table + lists H2D, plan, materialise, D2H
     ne = args.e2e_haplotypes
+    d2h_peak = pcie_d2h_peak(torch) if ne > 0 else None
     host_out = torch.empty(int((L + (4 << 20)) * max(ne, 1)) if ne > 0 else 16, dtype=torch.uint8, pin_memory=True)
     host_np = host_out.numpy()
     ref_pinned = torch.from_numpy(ref).pin_memory().numpy()
@@ -531,31 +686,57 @@ def main():
     if dist is not None:
         dist.all_reduce(e2e_val, op=dist.ReduceOp.SUM)
 
+    emission = None
+    if args.file_emission and rank == 0 and world == 1:
+        emission = file_emission_leg(splib, synth, work, local_rank)
+
     if rank == 0:
         peak, peak_kind = measured_peak_gbs()
-        per_rank_bases = bases_total
-        achieved = ALGO_BYTES_PER_BP * per_rank_bases / t_kernel / 1e9
+        per_launch_bases = bases_total / args.steps
+        per_launch_s = t_kernel / args.steps
+        algorithmic = ALGO_BYTES_PER_BP * per_launch_bases / per_launch_s / 1e9
+        traffic, cap = measured_traffic(args.batch, L, per_launch_bases)
+        # DRAM side of the launch: what ncu measured for this launch shape; without a matching capture, the bytes the kernel
+        # cannot avoid (every output byte written once + every reference byte read once from HBM)
+        dram_bytes = traffic if traffic is not None else per_launch_bases + L
+        achieved = dram_bytes / per_launch_s / 1e9
+        cfg = workload_config(L, args.batch, info["n_variants"], info["local_entries"])
         line = {"metric": "simulated haplotype Gbp/s", "value": value, "unit": "Gbp/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * t_step_max / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": workload, "haplotypes_per_step_per_gpu": args.batch, "n_variants": info["n_variants"],
-                           "variants_per_haplotype": round(info["local_entries"] / N_HAPLOTYPES, 1),
-                           "step": "genotype kernel + collision fixer + segment scan + materialisation kernel for one batch",
-                           "overlap": "none" if args.no_overlap else "rows G/C/N of batch s+1 on a second stream under the materialisation kernel of batch s",
-                           "l2": "inputs larger than L2 (>=31 GB written per step)", "sharding": "by individual, no collective"},
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
+                "arm": {"haplotypes_per_step_per_gpu": args.batch,
+                        "step": "genotype kernel + collision fixer + segment scan + tile table + materialisation kernel for one batch",
+                        "overlap": "none" if args.no_overlap else "rows G/C/N and the plan of batch s+1 on a second stream under the materialisation kernel of batch s",
+                        "sharding": "by individual; the one all-gather (carrier counts) runs before the timed region, see `collective`"},
                 "gpu_launches": int(launches),
+                "parity_spot_check": "ok",
+                "collective": collective,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": measured_traffic(args.batch, L), "kernel": "materialise_kernel", "peak_kind": peak_kind,
-                             "algorithmic_bytes_per_bp": ALGO_BYTES_PER_BP, "kernel_ms_per_step": 1e3 * t_kernel / args.steps,
-                             "genotype_call_ms_per_step": 1e3 * t_geno / args.steps, "plan_ms_per_step": 1e3 * t_plan / args.steps},
-                "setup_s": {"generate_inputs": round(t_gen, 2), "simulate_population_once": round(t_pop, 2)},
+                             "traffic": traffic, "traffic_source": ("ncu capture " + cap["capture"]) if cap else "no capture of this launch shape: output bytes + reference bytes",
+                             "kernel": "materialise_kernel", "peak_kind": peak_kind,
+                             "what": "DRAM bytes per launch / average launch duration (CUDA events on the launching stream) / measured copy peak",
+                             "algorithmic_bytes_per_bp": ALGO_BYTES_PER_BP, "algorithmic_achieved": algorithmic,
+                             "algorithmic_frac": algorithmic / peak,
+                             "l2_reuse": f"every reference byte is read by {args.batch} haplotypes of the launch; region-major tile order serves {args.batch - 1} of them from L2",
+                             "kernel_ms_per_step": 1e3 * per_launch_s, "bases_per_launch": per_launch_bases},
+                "per_rank": {"ms_per_step": [1e3 * x / args.steps for x in allr[:, 0]],
+                             "kernel_ms_per_step": [1e3 * x / args.steps for x in allr[:, 1]],
+                             "host_ms_in_population_genotypes": [1e3 * x / args.steps for x in allr[:, 3]],
+                             "host_ms_in_plan_haplotypes": [1e3 * x / args.steps for x in allr[:, 4]],
+                             "kernel_ms_per_step_max": 1e3 * t_kernel_max / args.steps},
+                "prologue": {"generate_inputs_s": round(t_gen, 2), "simulate_population_once_s": round(t_pop, 3),
+                             "rows_s": {k: round(v, 4) for k, v in prologue_rows.items()},
+                             "note": "rows A1-A3, S1, I, R1 are the replicated sequential prologue (host); G/C/N is the device part over all 1000 haplotypes"},
                 "e2e": {"value": float(e2e_val[0]), "unit": "Gbp/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "haplotypes_per_call": ne},
+                        "haplotypes_per_call": ne, "d2h_peak_GBps_measured": d2h_peak,
+                        "frac_of_d2h_peak": (float(e2e_val[0]) / world / d2h_peak) if d2h_peak else None},
                 "clocks": sampler.summary(), "wall_s_timed_region": t_wall}
         if reads_obj is not None:
             line["reads"] = reads_obj
         if bins_obj is not None:
             line["length_bins"] = bins_obj
+        if emission is not None:
+            line["file_emission"] = emission
         if world == 1 and not args.no_cpu_baseline:
             if reads_obj is not None:
                 rb = reads_cpu_baseline(synth, work)
@@ -568,6 +749,9 @@ def main():
     ctx.close()
     import shutil
     shutil.rmtree(work, ignore_errors=True)
+    barrier()
+    if local_rank == 0:
+        shutil.rmtree(shared, ignore_errors=True)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -130,6 +130,11 @@ int sp_population_local_lists(sp_ctx* ctx, int64_t* off, int32_t* ids);
 int sp_population_pre_collision_lists(sp_ctx* ctx, int64_t* off, int32_t* ids, int64_t ids_capacity, int64_t* n_ids);
 /* Draw-stream bookkeeping of the replicated prologue. */
 int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, int32_t* candidates);
+/* Wall-clock seconds of the last begin/finish by row of the hot-path table: [0] A1 loadReference (:93), [1] A2 model parsers
+ * (:95-97), [2] A3 loadPositions (:99), [3] S1 sampleVariants (:101), [4] G/C/N buildPopulation on the device (:104),
+ * [5] I assignInsertionStrings (:107-109), [6] R1 annotateVariantsWithRepeats (:111), [7] W buildVCF (:113), [8] Z serialize
+ * + histograms (:114-115). n_rows (may be NULL) = 9. */
+int sp_population_timing(sp_ctx* ctx, double* row_seconds, int32_t capacity, int32_t* n_rows);
 /* finish: AF := carriers/H and isActive from global_counts (NULL = the local counts are global), then
  * assignInsertionStrings, annotateVariantsWithRepeats, the individual VCFs of the local shard and, when
  * all_off/all_ids (CSR over ALL haplotypes) are given and write_joint_outputs!=0, the joint VCF, haplotype2variants.txt,

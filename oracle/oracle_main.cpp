@@ -46,6 +46,7 @@ int main(int argc, char** argv) {
                             sh.drawLog.candidates, (unsigned long long)sh.drawLog.steps_after_sampleVariants,
                             (unsigned long long)sh.drawLog.steps_after_buildPopulation,
                             (unsigned long long)sh.drawLog.steps_after_assignInsertionStrings, sh.lastVariant + 1, sh.N_HAPLOTYPES);
+                    for (size_t k = 0; k < sh.phaseNames.size(); k++) fprintf(f, "seconds_%s=%.6f\n", sh.phaseNames[k].c_str(), sh.phaseSeconds[k]);
                     fclose(f);
                 }
             }

@@ -83,6 +83,8 @@ struct SimulateHaplotypes {
     // Optional dump of the genotype matrix before collision fixing (row G of SURVEY.md §8a), one
     // line per haplotype, for kernel-level parity tests.
     std::string dumpPreCollisionFile;
+    std::vector<std::string> phaseNames;   // mainSimulate's wall-clock seconds per phase (reporting only)
+    std::vector<double> phaseSeconds;
 
     explicit SimulateHaplotypes(int64_t seed) : random(seed) {}
 

@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY. See simulate_haplotypes.h.
 // Truth VCFs, histograms, (de)serialisation and the two main() entry points.
 #include "simulate_haplotypes.h"
+#include <chrono>
 
 namespace oracle {
 
@@ -212,23 +213,28 @@ int SimulateHaplotypes::mainSimulate(const std::vector<std::string>& args) {
     const std::string OUTPUT_DIR = args[10];
     const int MAX_DISTANCE_TO_REPEAT_INTERVAL = 100;
     const int HISTOGRAM_BIN_SIZE = 100000;
-    loadReference(REFERENCE_FILE);
+    // wall-clock seconds per phase (bench.py's prologue / reference-arm report): phaseSeconds[k], names in phaseNames
+    auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t = now();
+    auto lap = [&](const char* name) { const double u = now(); phaseNames.push_back(name); phaseSeconds.push_back(u - t); t = u; };
+    loadReference(REFERENCE_FILE); lap("loadReference");
     model.deserializeStatistics(MODEL_DIR);
     model.deserializeRepeatIntervals(REPEAT_INTERVALS_FILE);
-    model.deserializeSegdups(SEGDUPS_FILE);
-    loadPositions(referenceLength, BuildModel::MAX_DISTANCE_SR);
+    model.deserializeSegdups(SEGDUPS_FILE); lap("deserializeModel");
+    loadPositions(referenceLength, BuildModel::MAX_DISTANCE_SR); lap("loadPositions");
     sampleVariants(ALLELE_FREQUENCY_THRESHOLD, N_VARIANTS_FREQUENT, jc::binarySearchStr(BuildModel::AF_NAMES, 6, POPULATION_NAME));
+    lap("sampleVariants");
     drawLog.steps_after_sampleVariants = random.steps;
     if (verbose) fprintf(stderr, "DONE  Total variants=%d. Frequent=%d Rare=%d\n", lastVariant + 1, nVariants_frequent, nVariants_rare);
     buildPopulation(N_INDIVIDUALS, ALLELE_FREQUENCY_THRESHOLD, OUTPUT_DIR);
-    buildVariant2haplotypes();
+    buildVariant2haplotypes(); lap("buildPopulation");
     loadInsertions(INSERTION_STRINGS_FILE, N_INSERTION_STRINGS, BuildModel::SV_LENGTH_QUANTUM);
-    assignInsertionStrings();
+    assignInsertionStrings(); lap("assignInsertionStrings");
     drawLog.steps_after_assignInsertionStrings = random.steps;
-    annotateVariantsWithRepeats(MAX_DISTANCE_TO_REPEAT_INTERVAL);
-    buildVCF(OUTPUT_DIR);
+    annotateVariantsWithRepeats(MAX_DISTANCE_TO_REPEAT_INTERVAL); lap("annotateVariantsWithRepeats");
+    buildVCF(OUTPUT_DIR); lap("buildVCF");
     serialize(OUTPUT_DIR + "/haplotype2variants.txt", OUTPUT_DIR + "/variants.txt");
-    printPositionHistogram(OUTPUT_DIR + "/histogram_startPositions.txt", HISTOGRAM_BIN_SIZE);
+    printPositionHistogram(OUTPUT_DIR + "/histogram_startPositions.txt", HISTOGRAM_BIN_SIZE); lap("serialize");
     return 0;
 }
 

@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "textio.h"
 #include <algorithm>
+#include "file_sink.h"
 
 namespace sp {
 void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride);
@@ -183,6 +184,84 @@ void load_population(sp_ctx* c, const char* h2v_file, const char* variants_file)
     upload_variants(c);
     upload_lists(c);
 }
+
+// Streams device bytes into files through a ring of pinned chunks: the caller's thread issues the D2H copies (stream
+// order), a writer thread waits for each chunk's event and appends it to the current file. One file at a time, in order.
+FileSink::FileSink(int device, int n_slots, int64_t chunk_bytes) : device_(device), chunk_(chunk_bytes), slots_((size_t)n_slots) {
+    for (Slot& s : slots_) {
+        SP_CUDA(cudaHostAlloc((void**)&s.buf, (size_t)chunk_, cudaHostAllocDefault));
+        SP_CUDA(cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming));
+    }
+    writer_ = std::thread([this] { this->run(); });
+}
+
+FileSink::~FileSink() {
+    { std::lock_guard<std::mutex> g(m_); stop_ = true; }
+    cv_.notify_all();
+    if (writer_.joinable()) writer_.join();
+    for (Slot& s : slots_) { if (s.buf) cudaFreeHost(s.buf); if (s.ev) cudaEventDestroy(s.ev); }
+    if (file_) fclose(file_);
+}
+
+void FileSink::run() {
+    cudaSetDevice(device_);
+    for (;;) {
+        Task t;
+        {
+            std::unique_lock<std::mutex> g(m_);
+            cv_.wait(g, [&] { return stop_ || !queue_.empty(); });
+            if (queue_.empty()) return;
+            t = queue_.front(); queue_.pop_front();
+        }
+        Slot& s = slots_[(size_t)t.slot];
+        bool ok = cudaEventSynchronize(s.ev) == cudaSuccess;
+        if (ok && !failed_) {
+            if (t.open) {
+                file_ = fopen(t.path.c_str(), "wb");
+                if (!file_) { std::lock_guard<std::mutex> g(m_); failed_ = true; error_ = "FileNotFoundException: " + t.path; }
+            }
+            if (file_ && fwrite(s.buf, 1, (size_t)t.bytes, file_) != (size_t)t.bytes) {
+                std::lock_guard<std::mutex> g(m_); failed_ = true; error_ = "IOException: short write " + t.path;
+            }
+            if (t.close && file_) { fclose(file_); file_ = nullptr; }
+        } else if (!ok) { std::lock_guard<std::mutex> g(m_); failed_ = true; error_ = "device-to-host copy failed"; }
+        { std::lock_guard<std::mutex> g(m_); s.busy = false; pending_--; }
+        cv_.notify_all();
+    }
+}
+
+void FileSink::write_file(const std::string& path, const uint8_t* d_src, int64_t n, cudaStream_t st) {
+    int64_t off = 0;
+    bool first = true;
+    do {
+        const int64_t nb = std::min(chunk_, n - off);
+        int slot;
+        {
+            std::unique_lock<std::mutex> g(m_);
+            cv_.wait(g, [&] { return !slots_[(size_t)next_].busy; });
+            if (failed_) throw Error(SP_ERR_JAVA_EXCEPTION, error_);
+            slot = next_; next_ = (next_ + 1) % (int)slots_.size();
+            slots_[(size_t)slot].busy = true; pending_++;
+        }
+        if (nb > 0) SP_CUDA(cudaMemcpyAsync(slots_[(size_t)slot].buf, d_src + off, (size_t)nb, cudaMemcpyDeviceToHost, st));
+        SP_CUDA(cudaEventRecord(slots_[(size_t)slot].ev, st));
+        off += nb;
+        {
+            std::lock_guard<std::mutex> g(m_);
+            queue_.push_back(Task{slot, nb, first, off >= n, path});
+        }
+        cv_.notify_all();
+        first = false;
+    } while (off < n);
+}
+
+void FileSink::drain() {
+    std::unique_lock<std::mutex> g(m_);
+    cv_.wait(g, [&] { return pending_ == 0; });
+    if (failed_) throw Error(SP_ERR_JAVA_EXCEPTION, error_);
+}
+
+void FileSink::finish() { drain(); }
 
 static void check_planned(sp_ctx* c, int32_t h) {
     if (c->plan_last < c->plan_first || h < c->plan_first || h > c->plan_last)
@@ -412,24 +491,19 @@ int sp_print_haplotypes(sp_ctx* ctx, int32_t first, int32_t last, const char* re
     SP_CUDA(cudaMemGetInfo(&free_b, &total_b));
     const int64_t per_hap = ctx->ref_len * 2 + (64 << 20);
     int32_t batch = (int32_t)std::max<int64_t>(1, std::min<int64_t>(64, (int64_t)(free_b / 2) / std::max<int64_t>(per_hap, 1)));
-    std::vector<uint8_t> host;
+    // Device -> pinned ring -> files: the copy engine fills chunk k+1 (and the copy kernel materialises the next batch)
+    // while a writer thread pushes chunk k into the page cache.
+    sp::FileSink sink(ctx->device, 6, 32ll << 20);
     for (int32_t a = first; a <= last; a += batch) {
         const int32_t b = std::min(last, a + batch - 1);
+        sink.drain();   // the slots are about to be overwritten: every copy out of them must have been issued AND done
         sp::plan_haplotypes(ctx, a, b, 1, nullptr, nullptr);
         sp::materialise(ctx);
-        for (int32_t h = a; h <= b; h++) {
-            const int64_t n = ctx->h_hap_len[h - a];
-            host.resize((size_t)n);
-            SP_CUDA(cudaMemcpyAsync(host.data(), ctx->d_out.p + (int64_t)(h - a) * ctx->slot_stride, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
-            SP_CUDA(cudaStreamSynchronize(ctx->stream));
-            const std::string path = std::string(output_dir) + "/haplotype_" + std::to_string(h) + ".fa";
-            FILE* f = fopen(path.c_str(), "wb");
-            if (!f) throw Error(SP_ERR_JAVA_EXCEPTION, "FileNotFoundException: " + path);
-            const size_t w = fwrite(host.data(), 1, (size_t)n, f);
-            fclose(f);
-            if (w != (size_t)n) throw Error(SP_ERR, "IOException: short write " + path);
-        }
+        for (int32_t h = a; h <= b; h++)
+            sink.write_file(std::string(output_dir) + "/haplotype_" + std::to_string(h) + ".fa",
+                            ctx->d_out.p + (int64_t)(h - a) * ctx->slot_stride, ctx->h_hap_len[h - a], ctx->stream);
     }
+    sink.finish();
     if (requested_last > last)
         throw Error(SP_ERR_JAVA_EXCEPTION, "ArrayIndexOutOfBoundsException: haplotype " + std::to_string(last + 1));
     SP_API_END

@@ -3,9 +3,21 @@
 #include "java_random.cuh"
 #include "textio.h"
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 
 namespace sp {
+
+namespace {
+struct Lap {   // seconds since the previous lap, added to a row's total
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void operator()(double& into) {
+        const auto u = std::chrono::steady_clock::now();
+        into += std::chrono::duration<double>(u - t).count();
+        t = u;
+    }
+};
+}  // namespace
 
 void free_population(sp_ctx* c) {
     if (!c->pop) return;
@@ -77,14 +89,19 @@ void population_begin(sp_ctx* c, const sp_population_args* a, int32_t first_h, i
     P.h0 = first_h; P.h1 = last_h + 1;
     P.keep_pre_collision = getenv("SYNTHPOP_KEEP_PRE_COLLISION") != nullptr;
 
+    Lap lap;
     load_reference_fasta(c, P.reference_file.c_str());                  // :93
+    lap(P.row_seconds[PopulationState::T_A1]);
     P.model.load_statistics(P.model_dir);                               // :95
     P.model.load_repeat_intervals(P.repeats_file);                      // :96
     P.model.load_segdups(P.segdups_file);                               // :97
+    lap(P.row_seconds[PopulationState::T_A2]);
     const int32_t L = (int32_t)c->ref_len;
     P.positions.build(P.model, c->h_ref.data(), L, MAX_DISTANCE_SR);    // :99
+    lap(P.row_seconds[PopulationState::T_A3]);
     sample_variants(P, c->seed, L);                                     // :101
     publish_variants(c, P);
+    lap(P.row_seconds[PopulationState::T_S1]);
     // nextDouble() <= AF  <=>  draw53 <= floor(AF * 2^53): both sides are exact in binary64
     P.h_thr.resize(P.n_variants);
     for (int32_t v = 0; v < P.n_variants; v++) {
@@ -96,6 +113,7 @@ void population_begin(sp_ctx* c, const sp_population_args* a, int32_t first_h, i
         P.h_thr[v] = t;
     }
     run_genotype_and_collisions(c, P);                                  // :104 (loops A and the collision fixer)
+    lap(P.row_seconds[PopulationState::T_GCN]);
     P.begun = true; P.finished = false;
 }
 
@@ -137,8 +155,11 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
         if (r.isActive) { if (r.alleleFrequency >= P.af_threshold) P.nVariants_frequent++; else P.nVariants_rare++; }
     }
     for (int32_t v = 0; v < V; v++) P.variants[v].alleleFrequency = ((double)(P.counts_global[v] - 1) + 1.0) / (double)H;
+    Lap lap;
     assign_insertion_strings(P, c->seed);                               // :107-109
+    lap(P.row_seconds[PopulationState::T_I]);
     annotate_variants_with_repeats(P, 100);                             // :111
+    lap(P.row_seconds[PopulationState::T_R1]);
     const bool skip_individual = (write_joint & 2) != 0;
     write_joint &= 1;
     if ((write_joint || !skip_individual) && (int64_t)c->h_ref.size() != c->ref_len)
@@ -149,7 +170,9 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
         write_joint_vcf(P, c->h_ref.data(), L);
     }
     if (!skip_individual) write_individual_vcfs(P, c->h_ref.data(), L, P.h0, P.h1 - 1, P.h_off.data(), P.h_ids.data(), P.h0);  // :1027-1066
+    lap(P.row_seconds[PopulationState::T_W]);
     if (write_joint) write_population_files(P);                        // :114
+    lap(P.row_seconds[PopulationState::T_Z]);
     // leave the context ready for sp_plan_haplotypes: variant table with payloads + haplotype lists
     publish_variants(c, P);
     c->n_haplotypes = H;
@@ -297,6 +320,14 @@ int sp_population_draw_log(sp_ctx* ctx, uint64_t* steps_after_sample_variants, i
     sp::PopulationState& P = pop_of(ctx);
     if (steps_after_sample_variants) *steps_after_sample_variants = P.steps_after_sampling;
     if (candidates) *candidates = P.candidates;
+    SP_API_END
+}
+
+int sp_population_timing(sp_ctx* ctx, double* row_seconds, int32_t capacity, int32_t* n_rows) {
+    SP_API_BEGIN
+    sp::PopulationState& P = pop_of(ctx);
+    if (n_rows) *n_rows = sp::PopulationState::T_N_ROWS;
+    for (int i = 0; row_seconds && i < capacity && i < sp::PopulationState::T_N_ROWS; i++) row_seconds[i] = P.row_seconds[i];
     SP_API_END
 }
 

@@ -64,6 +64,10 @@ struct PopulationState {
     std::vector<int32_t> all_ids;
     bool have_all_lists = false;
     bool begun = false, finished = false;
+
+    // wall-clock seconds per row of SURVEY.md §8a for the last begin/finish (sp_population_timing)
+    enum { T_A1 = 0, T_A2, T_A3, T_S1, T_GCN, T_I, T_R1, T_W, T_Z, T_N_ROWS };
+    double row_seconds[T_N_ROWS] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 void run_genotype_and_collisions(sp_ctx* c, PopulationState& P);

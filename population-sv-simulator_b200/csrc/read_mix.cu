@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "java_random.cuh"
 #include "reads.h"
+#include "file_sink.h"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
@@ -322,23 +323,11 @@ int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const cha
     }
     if (rc == SP_OK) rc = sp_reads_mix_finish(ctx, shuffle_seed, n_reads, file_bytes);
     if (rc != SP_OK) return rc;
-    if (output_file) {
+    if (output_file) {   // device -> pinned ring -> file, the writer thread overlapping the copies (csrc/file_sink.h)
         sp::ReadMixState& M = *ctx->mix;
-        struct Closer {  // the file and the pinned staging buffer are released on every path out of this block
-            FILE* f = nullptr;
-            uint8_t* stage = nullptr;
-            ~Closer() { if (f) fclose(f); if (stage) cudaFreeHost(stage); }
-        } io;
-        io.f = fopen(output_file, "wb");
-        if (!io.f) throw Error(SP_ERR, std::string("cannot write ") + output_file);
-        const int64_t chunk = 256ll << 20;
-        SP_CUDA(cudaMallocHost((void**)&io.stage, (size_t)std::min<int64_t>(chunk, std::max<int64_t>(M.out_bytes, 1))));
-        for (int64_t o = 0; o < M.out_bytes; o += chunk) {
-            const int64_t nb = std::min(chunk, M.out_bytes - o);
-            SP_CUDA(cudaMemcpyAsync(io.stage, M.d_out.p + o, (size_t)nb, cudaMemcpyDeviceToHost, ctx->stream));
-            SP_CUDA(cudaStreamSynchronize(ctx->stream));
-            if ((int64_t)fwrite(io.stage, 1, (size_t)nb, io.f) != nb) throw Error(SP_ERR, std::string("short write to ") + output_file);
-        }
+        sp::FileSink sink(ctx->device, 4, 64ll << 20);
+        sink.write_file(output_file, M.d_out.p, M.out_bytes, ctx->stream);
+        sink.finish();
     }
     SP_API_END
 }

@@ -95,6 +95,12 @@ def _p(dtype):
     return np.ctypeslib.ndpointer(dtype=dtype, flags="C_CONTIGUOUS")
 
 
+class AnnotateArgs(C.Structure):
+    """sp_annotate_args: positional argv of AnnotateVCF.main (src/AnnotateVCF.java:96-102)."""
+    _fields_ = [("input_files_list", C.c_char_p), ("min_distance", C.c_int32), ("max_distance", C.c_int32),
+                ("reference_file", C.c_char_p), ("repeat_intervals_file", C.c_char_p), ("segdups_file", C.c_char_p)]
+
+
 def load() -> C.CDLL:
     """dlopen the in-tree libsynthpop_cuda.so and declare every prototype of include/synthpop_cuda.h."""
     global _lib
@@ -150,6 +156,7 @@ def load() -> C.CDLL:
         "sp_population_pre_collision_lists": (C.c_int, [vp, vp, vp, i64, P(i64)]),
         "sp_population_draw_log": (C.c_int, [vp, P(C.c_uint64), P(i32)]),
         "sp_population_finish": (C.c_int, [vp, vp, vp, vp, i32]),
+        "sp_population_timing": (C.c_int, [vp, vp, i32, P(i32)]),
         "sp_reads_configure": (C.c_int, [vp, P(ReadArgs)]),
         "sp_reads_set_replay": (C.c_int, [vp, vp, i64, vp, i64]),
         "sp_reads_simulate_haplotype": (C.c_int, [vp, i32, i64, P(i64), P(i64), P(i64), P(i64)]),
@@ -354,6 +361,15 @@ class Context:
         nv, nh, ne, nf = C.c_int32(), C.c_int32(), C.c_int64(), C.c_int32()
         self._check(self.lib.sp_population_info(self.h, C.byref(nv), C.byref(nh), C.byref(ne), C.byref(nf)))
         return dict(n_variants=nv.value, n_haplotypes=nh.value, local_entries=ne.value, n_fixed=nf.value)
+
+    POPULATION_ROWS = ("A1_loadReference", "A2_model", "A3_loadPositions", "S1_sampleVariants", "GCN_buildPopulation",
+                       "I_assignInsertionStrings", "R1_annotateVariantsWithRepeats", "W_buildVCF", "Z_serialize")
+
+    def population_timing(self) -> dict:
+        """Wall-clock seconds of the last begin/finish per row of SURVEY.md §8a."""
+        out = np.zeros(len(self.POPULATION_ROWS), np.float64)
+        self._check(self.lib.sp_population_timing(self.h, _ptr(out), out.size, None))
+        return {k: float(v) for k, v in zip(self.POPULATION_ROWS, out)}
 
     def population_local_counts(self) -> np.ndarray:
         info = self.population_info()

@@ -97,11 +97,24 @@ def simulate_population_sharded(ctx, argv, dist=None, write_files: bool = True):
         local = torch.as_tensor(_DeviceInt32(ctx.population_counts_device(), V), device=device)  # zero-copy: the library's buffer
     else:
         local = torch.from_numpy(ctx.population_local_counts().copy())
-    counts = allgather_counts(local, dist).cpu().numpy().astype(np.int32)
+    # the ONE exchange of the path (north_star): all-gather of the per-variant carrier counts, timed on the device
+    ev = None
+    if nccl:
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        ev[0].record()
+    counts_t = allgather_counts(local, dist)
+    if nccl:
+        ev[1].record()
+    counts = counts_t.cpu().numpy().astype(np.int32)
     off, ids = ctx.population_local_lists(n_local)
     all_off, all_ids = allgather_lists(off, ids, dist, device)
+    timing = dict(counts_bytes_per_rank=int(V) * 4, lists_bytes_total=int(all_ids.size) * 4 + int(all_off.size) * 8)
+    if nccl:
+        ev[2].record()
+        torch.cuda.synchronize()
+        timing.update(counts_allgather_ms=ev[0].elapsed_time(ev[1]), lists_allgather_ms=ev[1].elapsed_time(ev[2]))
     if write_files:
         ctx.population_finish(counts, all_off if rank == 0 else None, all_ids if rank == 0 else None, 1 if rank == 0 else 0)
     else:
         ctx.population_finish(counts, None, None, 2)
-    return dict(first=first, last=last, counts=counts, n_variants=V, all_off=all_off, all_ids=all_ids)
+    return dict(first=first, last=last, counts=counts, n_variants=V, all_off=all_off, all_ids=all_ids, collective=timing)

@@ -200,26 +200,30 @@ def write_insertions(path: str, n: int, seed: int = GENERATOR_SEED, max_len: int
 
 
 def generate_population_inputs(root: str, length: int, seed: int = GENERATOR_SEED, n_insertions: int = 30000,
-                               max_sv_length: int | None = None, frac_frequent: float | None = None) -> SynthInputs:
+                               max_sv_length: int | None = None, frac_frequent: float | None = None,
+                               reuse: bool = False) -> SynthInputs:
+    """reuse=True: the files under `root` were already written by another process with the same arguments (the ranks of one
+    box share them); only the in-memory arrays are rebuilt."""
     os.makedirs(root, exist_ok=True)
     bases, rep, seg = random_reference(length, seed)
     ref = os.path.join(root, "reference.fa")
-    write_fasta(ref, "chr1", bases)
     repf = os.path.join(root, "repeatIntervals.txt")
-    with open(repf, "w") as f:
-        f.write(f"{rep.shape[0]}\n")
-        np.savetxt(f, rep, fmt="%d", delimiter=",")
     segf = os.path.join(root, "segdups.txt")
-    with open(segf, "w") as f:
-        f.write(f"{seg.shape[0]}\n")
-        np.savetxt(f, seg, fmt="%d", delimiter=",")
-    if max_sv_length is None:
-        max_sv_length = min(1000000, max(100, length // 40))
-    max_ins = min(10000, max(100, (length // 100) // 50 * 50))
     model_dir = os.path.join(root, "model")
-    write_model(model_dir, seed, max_sv_length=max_sv_length, max_ins_length=max_ins, frac_frequent=frac_frequent)
     insf = os.path.join(root, "insertions.txt")
-    write_insertions(insf, n_insertions, seed, max_len=max_ins)
+    if not reuse:
+        write_fasta(ref, "chr1", bases)
+        with open(repf, "w") as f:
+            f.write(f"{rep.shape[0]}\n")
+            np.savetxt(f, rep, fmt="%d", delimiter=",")
+        with open(segf, "w") as f:
+            f.write(f"{seg.shape[0]}\n")
+            np.savetxt(f, seg, fmt="%d", delimiter=",")
+        if max_sv_length is None:
+            max_sv_length = min(1000000, max(100, length // 40))
+        max_ins = min(10000, max(100, (length // 100) // 50 * 50))
+        write_model(model_dir, seed, max_sv_length=max_sv_length, max_ins_length=max_ins, frac_frequent=frac_frequent)
+        write_insertions(insf, n_insertions, seed, max_len=max_ins)
     return SynthInputs(root=root, reference_file=ref, model_dir=model_dir, repeat_intervals_file=repf,
                        segdups_file=segf, insertions_file=insf, n_insertions=n_insertions,
                        reference_length=length, extra={"bases": bases, "repeat_intervals": rep, "segdups": seg})
