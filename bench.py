@@ -86,7 +86,7 @@ CCS_CLI = ["--length-min", "5000", "--length-max", "30000", "--accuracy-min", "0
 READ_ALGO_BYTES_PER_BASE = 2.0  # 1 B of haplotype read + 1 B of read written per emitted base
 
 
-def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, quality="phred"):
+def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, quality="phred", resample=True):
     """BASELINE configs[3] on this GPU's shard: pbsim2-model CCS reads at `depth`x over `n_haps` chr1-sized haplotypes that
     were materialised on the device and never leave it. Returns the `reads` object of the bench line."""
     model = os.path.join(work, "P6C4_synthetic.model")
@@ -94,7 +94,8 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
     args, _ = splib.ReadArgs.from_options(CCS_CLI + ["--depth", str(depth), "--hmm_model", model, "--seed", "42"],
                                           stream_mode=splib.READS_PER_READ_STREAMS)
     ctx.reads_configure(args)
-    ctx.population_genotypes(first_hap, first_hap + n_haps - 1)   # rows G/C/N for these haplotypes
+    if resample:
+        ctx.population_genotypes(first_hap, first_hap + n_haps - 1)   # rows G/C/N for these haplotypes
     ctx.plan_haplotypes(first_hap, first_hap + n_haps - 1, False)
     ctx.materialise()
     ctx.synchronize()
@@ -532,6 +533,9 @@ def main():
     # carrier counts, then of the lists for the joint outputs), checked against the same run done by this rank alone
     collective = None
     if dist is not None:
+        warm = torch.zeros(world * 16, dtype=torch.int32, device="cuda")   # communicator set-up is not the exchange
+        dist.all_gather_into_tensor(warm, warm[:16].clone())
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
         res = sharded.simulate_population_sharded(ctx, argv, dist, write_files=False)
         t_sharded = time.perf_counter() - t0
@@ -655,6 +659,22 @@ def main():
             reads_obj["value"] = float(tb[0]) / float(tr[0]) / 1e9
             reads_obj["wall_s"] = float(tr[0])
 
+    # BASELINE configs[4] (row T, an extension: the reference's trios are real families): a child of two simulated parents,
+    # its truth VCF, its 30x reads mixed and cut into the 10x/20x/30x prefixes
+    trio_obj = None
+    if args.read_haplotypes > 0 and rank == 0 and world == 1:
+        peak, _ = measured_peak_gbs()
+        t0 = time.perf_counter()
+        child = ctx.trio_add_child(3, 8, 42, write_vcf=True)
+        t_child = time.perf_counter() - t0
+        h0 = child["child_first_haplotype"]
+        r = reads_leg(ctx, splib, synth, work, h0, 2, args.read_depth, peak, torch, args.read_quality, resample=False)
+        trio_obj = {"what": "sp_trio_add_child (one nextBoolean() per parent, truth VCF by the buildVCF merge) + the child's reads as in `reads`",
+                    "father_individual": 3, "mother_individual": 8, "child_haplotypes": [h0, h0 + 1], "inherited": [child["from_father_haplotype"], child["from_mother_haplotype"]],
+                    "add_child_and_vcf_s": round(t_child, 4), "child_vcf_bytes": os.path.getsize(os.path.join(out_dir, f"groundTruth_individual_{h0}.vcf")),
+                    "reads_gbp_s": r["value"], "reads_kernel_gbp_s": r["kernel_gbp_s"], "reads": r["reads"], "bases": r["bases"],
+                    "mix": r["mix"], "parity": "unpinned by construction (nothing in the reference derives a child); every piece is the oracle-pinned row it reuses"}
+
     # row D leg (rank 0 only: the same work would run on every GPU)
     bins_obj = None
     if args.length_bins and rank == 0:
@@ -735,6 +755,8 @@ def main():
             line["reads"] = reads_obj
         if bins_obj is not None:
             line["length_bins"] = bins_obj
+        if trio_obj is not None:
+            line["trio"] = trio_obj
         if emission is not None:
             line["file_emission"] = emission
         if world == 1 and not args.no_cpu_baseline:

@@ -44,6 +44,12 @@ int sp_set_population_stream(sp_ctx* ctx, void* cuda_stream);
 /* Number of kernels this library launched on ctx since creation (bench.py's gpu_launches). */
 int64_t sp_kernel_launches(const sp_ctx* ctx);
 
+/* Test hooks (no device work): the library's Double.toString (JDK >= 19 rules: "AF=", variants.txt) and
+ * NumberFormat.getInstance() with 4 fraction digits ("REPEATS_FRACTION=", src/SimulateHaplotypes.java:1010-1011, :1278).
+ * Return the string length. */
+int sp_test_double_to_string(double x, char* out, int32_t capacity);
+int sp_test_number_format4(double x, char* out, int32_t capacity);
+
 /* ---- row A1: reference ------------------------------------------------------------------------------ */
 /* SimulateHaplotypes.loadReference(String) (src/SimulateHaplotypes.java:119-134): skip one header line, trim and
  * concatenate the rest; bytes go to HBM once. */
@@ -303,6 +309,29 @@ int sp_annotate_file(sp_ctx* ctx, const char* input_vcf, const char* output_vcf,
                      int64_t* n_annotated);
 /* Seconds of the last load, device milliseconds of the last file's kernel, records annotated since the load. */
 int sp_annotate_timing(sp_ctx* ctx, double* load_seconds, double* last_kernel_ms, int64_t* records_total);
+
+/* ---- BuildReadLengthBins, Fastq2LengthHistogram ------------------------------------------------ */
+/* Positional argv of BuildReadLengthBins.main (src/BuildReadLengthBins.java:21-27). Writes <prefix><i>.bin for i in
+ * [0, N_BINS), N_BINS = (MAX_READ_LENGTH+BIN_LENGTH-1)/BIN_LENGTH (:28): the records of all listed FASTQ files whose
+ * sequence length falls in bin i (the last bin takes everything longer, :57-58), permuted by the reference's Fisher-Yates
+ * with `new Random(seed)` of the context shared by all bins (:95-99, :108-116; bins with fewer than three records keep their
+ * input order and draw nothing); <prefix>.histogram (:77-84) and <prefix>.stats (printStats :139-208). These are the
+ * files sp_sample_reads_from_bins / sp_length_bins_load consume. */
+typedef struct sp_build_bins_args {
+    const char* input_files_list;    /* args[0]: one FASTQ path per line */
+    int32_t bin_length;              /* args[1] */
+    int32_t max_read_length;         /* args[2] */
+    int64_t genome_length_haploid;   /* args[3] */
+    const char* output_prefix;       /* args[4] */
+} sp_build_bins_args;
+int sp_build_read_length_bins(sp_ctx* ctx, const sp_build_bins_args* args);
+/* Fastq2LengthHistogram.main (src/Fastq2LengthHistogram.java:11-51): FASTQ_FILE BIN_LENGTH MAX_READ_LENGTH
+ * OUTPUT_FILE_HISTOGRAM OUTPUT_FILE_MAX. */
+int sp_fastq2length_histogram(sp_ctx* ctx, const char* fastq_file, int32_t bin_length, int32_t max_read_length,
+                              const char* output_file_histogram, const char* output_file_max);
+/* Device milliseconds of the last sp_build_read_length_bins: line index + binning, draws + swap forest, gather copy; records
+ * and bytes written. Outputs may be NULL. */
+int sp_build_bins_timing(sp_ctx* ctx, double* index_ms, double* shuffle_ms, double* copy_ms, int64_t* n_records, int64_t* n_bytes);
 
 #ifdef __cplusplus
 }

@@ -96,14 +96,39 @@ inline std::string doubleToString(double d) {
     if (std::isinf(d)) return d > 0 ? "Infinity" : "-Infinity";
     if (d == 0.0) return std::signbit(d) ? "-0.0" : "0.0";
     char buf[64];
-    int prec;
-    for (prec = 1; prec < 17; prec++) {  // at least two significant digits (4.9E-324)
+    // The shortest decimal that reads back as d, at least two significant digits (4.9E-324). It is not always the
+    // correctly rounded one: next to a power of two the gap below is half the gap above, and the nearest n-digit decimal
+    // can fall outside the narrow side while its neighbour inside the wide side still reads back (2^-44 =
+    // 5.6843418860808015e-14 prints as 5.684341886080802E-14). So at every length the rounded decimal and its two
+    // neighbours in the last place are tried, and of those that read back the one closest to d wins.
+    std::string best;
+    for (int prec = 1; prec <= 16 && best.empty(); prec++) {
         snprintf(buf, sizeof buf, "%.*e", prec, d);
-        if (strtod(buf, nullptr) == d) break;
+        const std::string r(buf);
+        const size_t ep = r.find('e');
+        long double bestDist = 0;
+        for (int k = 0; k < 3; k++) {
+            const int delta = k == 0 ? 0 : (k == 1 ? -1 : 1);   // the correctly rounded one first: it wins a tie (half-even, as the JDK)
+            std::string c = r;
+            if (delta != 0) {   // one unit in the last place of the mantissa, as decimal string arithmetic
+                std::string m;
+                for (size_t i = 0; i < ep; i++) if (c[i] != '.' && c[i] != '-') m.push_back(c[i]);
+                long long v = atoll(m.c_str()) + delta;
+                int e10 = atoi(c.c_str() + ep + 1);
+                std::string mv = std::to_string(v);
+                if (mv.size() > m.size()) { e10++; mv.pop_back(); }            // 9.99 + 0.01 -> 10.0
+                else if (mv.size() < m.size()) { e10--; mv.push_back('9'); }    // 1.00 - 0.01 -> 0.99 -> 9.99e-1 (one more 9 keeps the length)
+                snprintf(buf, sizeof buf, "%s%c.%se%d", d < 0 ? "-" : "", mv[0], mv.c_str() + 1, e10);
+                c = buf;
+            }
+            if (strtod(c.c_str(), nullptr) != d) continue;
+            const long double dist = fabsl(strtold(c.c_str(), nullptr) - (long double)d);
+            if (best.empty() || dist < bestDist) { best = c; bestDist = dist; }
+        }
     }
-    snprintf(buf, sizeof buf, "%.*e", prec, d);
+    if (best.empty()) { snprintf(buf, sizeof buf, "%.16e", d); best = buf; }
     // parse "[-]D.DDDDe[+-]XX"
-    std::string s(buf);
+    std::string s(best);
     bool neg = s[0] == '-';
     if (neg) s = s.substr(1);
     size_t epos = s.find('e');

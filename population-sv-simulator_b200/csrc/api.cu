@@ -13,44 +13,67 @@ void free_length_bins(sp_ctx* c);
 void free_read_mix(sp_ctx* c);
 void free_annotate(sp_ctx* c);
 
+// Double.toString (JDK >= 19): the shortest decimal (at least two digits) that reads back as d and, among those of that
+// length, the one closest to d. Worked from the EXACT expansion of d (glibc's printf is exact at any precision): at length n
+// the only candidates are the expansion cut after n digits and that value plus one unit in the last place; which of the two
+// is closer is read off the digits that were cut.
 std::string java_double_to_string(double d) {
     if (d != d) return "NaN";
     if (d == 1.0 / 0.0) return "Infinity";
     if (d == -1.0 / 0.0) return "-Infinity";
     if (d == 0.0) return std::signbit(d) ? "-0.0" : "0.0";
-    char buf[64];
-    int prec = 1;  // at least two significant digits (Double.MIN_VALUE prints as 4.9E-324)
-    for (; prec < 17; prec++) {
-        snprintf(buf, sizeof buf, "%.*e", prec, d);
-        if (strtod(buf, nullptr) == d) break;
-    }
-    snprintf(buf, sizeof buf, "%.*e", prec, d);
-    char* e = strchr(buf, 'e');
-    const int exp10 = atoi(e + 1);
+    const bool neg = d < 0;
+    const double ad = neg ? -d : d;
+    char ex[900];
+    snprintf(ex, sizeof ex, "%.800e", ad);   // 801 significant digits: more than any double has
+    std::string all;
+    const char* e = strchr(ex, 'e');
+    for (const char* q = ex; q < e; q++) if (*q != '.') all.push_back(*q);
+    int exp10 = atoi(e + 1);
     std::string digits;
-    bool neg = false;
-    for (char* q = buf; q < e; q++) {
-        if (*q == '-') neg = true;
-        else if (*q != '.') digits.push_back(*q);
+    int dexp = exp10;
+    for (size_t n = 2; n <= 17 && digits.empty(); n++) {
+        const std::string lo = all.substr(0, n);
+        std::string hi = lo;   // lo + 1 unit in the last place
+        int hexp = exp10;
+        {
+            int k = (int)n - 1;
+            while (k >= 0 && hi[(size_t)k] == '9') hi[(size_t)k--] = '0';
+            if (k >= 0) hi[(size_t)k]++; else { hi = "1" + hi.substr(0, n - 1); hexp++; }
+        }
+        auto reads_back = [&](const std::string& m, int x) {
+            const std::string t = m.substr(0, 1) + "." + m.substr(1) + "e" + std::to_string(x);
+            return strtod(t.c_str(), nullptr) == ad;
+        };
+        const bool lo_ok = reads_back(lo, exp10), hi_ok = reads_back(hi, hexp);
+        if (!lo_ok && !hi_ok) continue;
+        bool take_hi = hi_ok && !lo_ok;
+        if (lo_ok && hi_ok) {   // the cut-off tail against one half: above -> hi is closer
+            const std::string tail = all.substr(n);
+            if (tail[0] > '5') take_hi = true;
+            else if (tail[0] == '5') take_hi = tail.find_first_not_of('0', 1) != std::string::npos || ((lo[n - 1] - '0') & 1);
+        }
+        digits = take_hi ? hi : lo;
+        dexp = take_hi ? hexp : exp10;
     }
+    if (digits.empty()) { digits = all.substr(0, 17); dexp = exp10; }
     while (digits.size() > 1 && digits.back() == '0') digits.pop_back();
     std::string out = neg ? "-" : "";
-    const double ad = d < 0 ? -d : d;
     if (ad >= 1e-3 && ad < 1e7) {
-        if (exp10 >= 0) {
-            for (int i = 0; i <= exp10; i++) out.push_back(i < (int)digits.size() ? digits[i] : '0');
+        if (dexp >= 0) {
+            for (int i = 0; i <= dexp; i++) out.push_back(i < (int)digits.size() ? digits[(size_t)i] : '0');
             out.push_back('.');
-            if ((int)digits.size() > exp10 + 1) out += digits.substr(exp10 + 1); else out.push_back('0');
+            if ((int)digits.size() > dexp + 1) out += digits.substr((size_t)dexp + 1); else out.push_back('0');
         } else {
             out += "0.";
-            out.append((size_t)(-exp10 - 1), '0');
+            out.append((size_t)(-dexp - 1), '0');
             out += digits;
         }
     } else {
         out.push_back(digits[0]);
         out.push_back('.');
         if (digits.size() > 1) out += digits.substr(1); else out.push_back('0');
-        out += "E" + std::to_string(exp10);
+        out += "E" + std::to_string(dexp);
     }
     return out;
 }
@@ -275,7 +298,20 @@ using sp::Error;
 
 extern "C" {
 
-const char* sp_version(void) { return "synthpop-cuda 0.1 (sm_100a)"; }
+const char* sp_version(void) { return "synthpop-cuda 0.2 (sm_100a)"; }
+
+// Test hooks: the product's own Double.toString / NumberFormat(4 digits) restatements (host text formatting of rows W, Z
+// and AnnotateVCF), so that the known-answer vectors run against this library and not only against the oracle's copy.
+int sp_test_double_to_string(double x, char* out, int32_t capacity) {
+    const std::string s = sp::java_double_to_string(x);
+    snprintf(out, (size_t)capacity, "%s", s.c_str());
+    return (int)s.size();
+}
+int sp_test_number_format4(double x, char* out, int32_t capacity) {
+    const std::string s = sp::java_number_format4(x);
+    snprintf(out, (size_t)capacity, "%s", s.c_str());
+    return (int)s.size();
+}
 
 int sp_create(sp_ctx** out, int device, int64_t seed) {
     if (!out) return SP_ERR_ARG;

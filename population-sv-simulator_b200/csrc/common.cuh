@@ -181,6 +181,11 @@ struct sp_ctx {
 
     // §8(f) rank 2: AnnotateVCF (row A3's interval sets resident in HBM)
     sp::AnnotateState* annot = nullptr;
+
+    // §8(f) rank 3: BuildReadLengthBins — device milliseconds of the last call (line index + binning, draws + swap forest,
+    // gather copy), records and bytes written
+    double bb_ms[3] = {0.0, 0.0, 0.0};
+    int64_t bb_records = 0, bb_bytes = 0;
 };
 
 // Entry/exit of every extern "C" function: bind the context's device (failing loudly), turn exceptions into codes.

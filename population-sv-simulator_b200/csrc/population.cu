@@ -164,17 +164,17 @@ void population_finish(sp_ctx* c, const int32_t* global_counts, const int64_t* a
     write_joint &= 1;
     if ((write_joint || !skip_individual) && (int64_t)c->h_ref.size() != c->ref_len)
         throw Error(SP_ERR_ARG, "the VCF writers need the host copy of the reference this population was begun on");
-    if (write_joint) {
-        if (!P.have_all_lists) throw Error(SP_ERR_ARG, "the joint outputs need every haplotype's list");
-        write_histograms(P, L);
-        write_joint_vcf(P, c->h_ref.data(), L);
-    }
-    if (!skip_individual) write_individual_vcfs(P, c->h_ref.data(), L, P.h0, P.h1 - 1, P.h_off.data(), P.h_ids.data(), P.h0);  // :1027-1066
+    if (write_joint && !P.have_all_lists) throw Error(SP_ERR_ARG, "the joint outputs need every haplotype's list");
+    // the variant table with its payloads goes to the device now: the VCF gather reads the INS payloads from there, and the
+    // context is left ready for sp_plan_haplotypes
+    publish_variants(c, P);
+    if (write_joint) write_histograms(P, L);
+    lap(P.row_seconds[PopulationState::T_Z]);
+    if (write_joint || !skip_individual)                               // :113 buildVCF, bytes gathered on the device
+        write_vcfs_device(c, P, write_joint != 0, !skip_individual, P.h0, P.h1 - 1, P.h_off.data(), P.h_ids.data(), P.h0);
     lap(P.row_seconds[PopulationState::T_W]);
     if (write_joint) write_population_files(P);                        // :114
     lap(P.row_seconds[PopulationState::T_Z]);
-    // leave the context ready for sp_plan_haplotypes: variant table with payloads + haplotype lists
-    publish_variants(c, P);
     c->n_haplotypes = H;
     if (P.have_all_lists) { c->h_list_off = P.all_off; c->h_list_ids = P.all_ids; }
     else {
@@ -218,7 +218,7 @@ void trio_add_child(sp_ctx* c, int32_t father, int32_t mother, int64_t seed, int
     upload_context_lists(c);
     if (write_vcf && (int64_t)c->h_ref.size() != c->ref_len)
         throw Error(SP_ERR_ARG, "the VCF writers need the host copy of the reference this population was begun on");
-    if (write_vcf) write_individual_vcfs(P, c->h_ref.data(), (int32_t)c->ref_len, H, H + 1, c->h_list_off.data(), c->h_list_ids.data(), 0);
+    if (write_vcf) write_vcfs_device(c, P, false, true, H, H + 1, c->h_list_off.data(), c->h_list_ids.data(), 0);
     if (child_first) *child_first = H;
     if (from_father) *from_father = hf;
     if (from_mother) *from_mother = hm;

@@ -75,9 +75,8 @@ void fetch_host_lists(sp_ctx* c, PopulationState& P);
 void sample_variants(PopulationState& P, int64_t seed, int32_t reference_length);
 void assign_insertion_strings(PopulationState& P, int64_t seed);
 void annotate_variants_with_repeats(PopulationState& P, int maxDistance);
-void write_joint_vcf(const PopulationState& P, const uint8_t* ref, int32_t L);
-void write_individual_vcfs(const PopulationState& P, const uint8_t* ref, int32_t L, int32_t h_first, int32_t h_last,
-                           const int64_t* off, const int32_t* ids, int32_t base);
+void write_vcfs_device(sp_ctx* c, const PopulationState& P, bool write_joint, bool individuals, int32_t h_first, int32_t h_last,
+                       const int64_t* off, const int32_t* ids, int32_t base);
 void write_population_files(const PopulationState& P);
 void write_histograms(const PopulationState& P, int32_t L);
 void load_reference_fasta(sp_ctx* c, const char* path);

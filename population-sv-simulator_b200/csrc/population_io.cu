@@ -1,6 +1,6 @@
-// Byte-exact writers of SimulateHaplotypes' outputs (rows W and Z of SURVEY.md §8a): groundTruth_joint.vcf,
-// groundTruth_individual_<2k>.vcf, haplotype2variants.txt, variants.txt and the two histograms
-// (reference src/SimulateHaplotypes.java:707-717, :1005-1144, :1243-1292).
+// Byte-exact writers of SimulateHaplotypes' small outputs (row Z of SURVEY.md §8a): haplotype2variants.txt, variants.txt
+// and the two histograms (reference src/SimulateHaplotypes.java:707-717, :1104-1144, :1281-1292). The VCFs (row W) are
+// assembled on the device: csrc/population_vcf.cu.
 #include "population.h"
 #include "textio.h"
 #include <algorithm>
@@ -29,120 +29,6 @@ struct Out {
     }
 };
 }  // namespace
-
-// Variant.writeVCF :1243-1279
-static void write_vcf_record(Out& o, const PopulationState& P, const uint8_t* ref, int32_t L, int32_t id) {
-    const VariantRec& v = P.variants[id];
-    auto char_at = [&](int64_t p) -> char {
-        if (p < 0 || p >= L) throw Error(SP_ERR_JAVA_EXCEPTION, "StringIndexOutOfBoundsException: index " + std::to_string(p));
-        return (char)ref[p];
-    };
-    o.s("chr1\t");
-    if (v.svType == SP_DEL) {
-        o.i(v.position); o.c('\t');
-        o.s("simulated_"); o.i(id); o.c('\t');
-        const int64_t b = (int64_t)v.position - 1, e = (int64_t)v.position + v.length;
-        if (b < 0 || e > L || b > e)
-            throw Error(SP_ERR_JAVA_EXCEPTION, "StringIndexOutOfBoundsException: begin " + std::to_string(b) + ", end " + std::to_string(e) + ", length " + std::to_string(L));
-        o.b(ref + b, (size_t)(e - b)); o.c('\t');
-        o.c(char_at(b)); o.c('\t');
-        o.s("999\tPASS\t");
-        o.s("END="); o.i((int64_t)v.position + v.length); o.c(';');
-        o.s("SVLEN="); o.i(-(int64_t)v.length); o.c(';');
-    } else if (v.svType == SP_INS) {
-        o.i((int64_t)v.position + 1); o.c('\t');
-        o.s("simulated_"); o.i(id); o.c('\t');
-        o.c(char_at(v.position)); o.c('\t');
-        o.c(char_at(v.position));
-        if (!v.hasSequence) throw Error(SP_ERR_JAVA_EXCEPTION, "NullPointerException: INS without sequence");
-        o.b(P.payload.data() + v.seq_off, (size_t)v.seq_len); o.c('\t');
-        o.s("999\tPASS\t");
-        o.s("END="); o.i((int64_t)v.position + 1); o.c(';');
-        o.s("SVLEN="); o.i(v.length); o.c(';');
-    } else {
-        o.i((int64_t)v.position + 1); o.c('\t');
-        o.s("simulated_"); o.i(id); o.c('\t');
-        o.c(char_at(v.position)); o.c('\t');
-        o.c('<'); o.s(SV_TYPE_NAMES[v.svType]); o.s(">\t");
-        o.s("999\tPASS\t");
-        o.s("END="); o.i((int64_t)v.position + v.length); o.c(';');
-    }
-    o.s("SVTYPE="); o.s(SV_TYPE_NAMES[v.svType]); o.c(';');
-    o.s("AF="); o.s(java_double_to_string(v.alleleFrequency)); o.c(';');
-    o.s("REPEATS_START="); o.i(v.intervalType_start); o.c(';');
-    o.s("REPEATS_END="); o.i(v.intervalType_end); o.c(';');
-    o.s("REPEATS_FRACTION="); o.s(java_number_format4(((double)v.intervalSurface) / v.length));
-}
-
-// printVcfHeader :1077-1096
-static void write_vcf_header(Out& o, int32_t L, bool genotype, const std::string& sample) {
-    o.s("##fileformat=VCFv4.2\n");
-    o.s("##contig=<ID=chr1,length="); o.i(L); o.s(">\n");
-    o.s("##ALT=<ID=INS,Description=\"Insertion\">\n"
-        "##ALT=<ID=DEL,Description=\"Deletion\">\n"
-        "##ALT=<ID=DUP,Description=\"Duplication\">\n"
-        "##ALT=<ID=INV,Description=\"Inversion\">\n"
-        "##FILTER=<ID=PASS,Description=\"All filters passed\">\n"
-        "##INFO=<ID=END,Number=1,Type=Integer,Description=\"End position of structural variation\">\n"
-        "##INFO=<ID=SVTYPE,Number=1,Type=String,Description=\"Type of structural variant\">\n"
-        "##INFO=<ID=SVLEN,Number=1,Type=Integer,Description=\"Length of structural variation\">\n"
-        "##INFO=<ID=AF,Number=1,Type=Float,Description=\"Allele Frequency\">\n"
-        "##INFO=<ID=REPEATS_START,Number=1,Type=Integer,Description=\"Repetitive context around the first position\">\n"
-        "##INFO=<ID=REPEATS_END,Number=1,Type=Integer,Description=\"Repetitive context around the last position\">\n"
-        "##INFO=<ID=REPEATS_FRACTION,Number=1,Type=Float,Description=\"Fraction of the SV covered by repeats of any type\">\n"
-        "##FORMAT=<ID=GT,Number=1,Type=String,Description=\"Genotype\">\n"
-        "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO");
-    if (genotype) { o.s("\tFORMAT\t"); o.s(sample); }
-    o.c('\n');
-}
-
-// Joint VCF (:1014-1024). all_off/all_ids: CSR over ALL haplotypes (needed for ";HAPLOTYPES=").
-void write_joint_vcf(const PopulationState& P, const uint8_t* ref, int32_t L) {
-    const int32_t H = P.n_haplotypes_total, V = P.n_variants;
-    // variant2haplotypes (:967-985): transpose, haplotypes ascending
-    std::vector<int64_t> voff((size_t)V + 1, 0);
-    for (int64_t k = 0; k < (int64_t)P.all_ids.size(); k++) voff[P.all_ids[k] + 1]++;
-    for (int32_t v = 0; v < V; v++) voff[v + 1] += voff[v];
-    std::vector<int32_t> v2h(P.all_ids.size());
-    std::vector<int64_t> cur(voff.begin(), voff.end() - 1);
-    for (int32_t h = 0; h < H; h++)
-        for (int64_t k = P.all_off[h]; k < P.all_off[h + 1]; k++) v2h[cur[P.all_ids[k]]++] = h;
-    Out o(P.output_dir + "/groundTruth_joint.vcf");
-    write_vcf_header(o, L, false, "");
-    for (int32_t v = 0; v < V; v++) {
-        if (!P.variants[v].isActive) continue;
-        write_vcf_record(o, P, ref, L, v);
-        o.s(";HAPLOTYPES=");
-        for (int64_t k = voff[v]; k < voff[v + 1]; k++) {
-            if (k > voff[v]) o.c(',');
-            o.i(v2h[k]);
-        }
-        o.c('\n');
-    }
-    o.close();
-}
-
-// Individual VCFs (:1027-1066) for haplotype pairs (i,i+1), i even, inside [h_first, h_last]; lists from a CSR
-// whose row 0 is haplotype `base`.
-void write_individual_vcfs(const PopulationState& P, const uint8_t* ref, int32_t L, int32_t h_first, int32_t h_last,
-                           const int64_t* off, const int32_t* ids, int32_t base) {
-    for (int32_t i = h_first + (h_first & 1); i + 1 <= h_last; i += 2) {
-        Out o(P.output_dir + "/groundTruth_individual_" + std::to_string(i) + ".vcf");
-        write_vcf_header(o, L, true, "individual_" + std::to_string(i));
-        const int32_t* a = ids + off[i - base];
-        const int32_t* b = ids + off[i + 1 - base];
-        const int64_t na = off[i + 1 - base] - off[i - base], nb = off[i + 2 - base] - off[i + 1 - base];
-        int64_t j = 0, k = 0;
-        while (j < na && k < nb) {
-            if (a[j] < b[k]) { write_vcf_record(o, P, ref, L, a[j]); o.s("\tGT\t1|0\n"); j++; }
-            else if (b[k] < a[j]) { write_vcf_record(o, P, ref, L, b[k]); o.s("\tGT\t0|1\n"); k++; }
-            else { write_vcf_record(o, P, ref, L, a[j]); o.s("\tGT\t1|1\n"); j++; k++; }
-        }
-        while (j < na) { write_vcf_record(o, P, ref, L, a[j]); o.s("\tGT\t1|0\n"); j++; }
-        while (k < nb) { write_vcf_record(o, P, ref, L, b[k]); o.s("\tGT\t0|1\n"); k++; }
-        o.close();
-    }
-}
 
 // serialize :1123-1144, Variant.serialize :1281-1292
 void write_population_files(const PopulationState& P) {

@@ -296,9 +296,10 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
                     const uint32_t sh = 8 * (pos & 3);
                     const int qv = (qw[(pos >> 2) * 32] >> sh) & 255u;
                     if (v < s_thre[qv]) {
-                        const uint32_t d = dw[(pos >> 2) * 32];
-                        if (((d >> sh) & 255u) == 255u) job_error(J, 3, r);
-                        dw[(pos >> 2) * 32] = d + (1u << sh);
+                        // one more deletion after position pos: a fire-and-forget reduction (no load to wait for). A
+                        // counter byte that wraps (more than 255 deletions at one position) shows up as a wrong total in
+                        // the pass over the bases below.
+                        asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(dw + (pos >> 2) * 32), "r"(1u << sh) : "memory");
                         num++;
                     }
                 }
@@ -327,6 +328,7 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     bool drop = false;
     int32_t t = 0;  // template index: advances with every base except after an insertion, and over deleted bases
     uint32_t wq = 0, wd = 0;
+    int32_t dsum = 0;   // deletions met along the read: must come to ndel
     __syncwarp(mask);
 #pragma unroll 1
     for (int32_t k = 0;; k++) {
@@ -336,6 +338,7 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
             if ((k & 3) == 0) { wq = qw[(k >> 2) * 32]; wd = ndel > 0 ? dw[(k >> 2) * 32] : 0u; }
             const int qv = wq & 255u; wq >>= 8;
             const int32_t dc = wd & 255u; wd >>= 8;
+            dsum += dc;
             const uint8_t nt = Tm.at(t);
             const int32_t d = (int32_t)(S.next() % 1000000u);
             uint8_t outc = nt;
@@ -364,6 +367,7 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     }
     __syncwarp(mask);
     if (bad) { J.dropped[r] = 1; J.used[r] = 0; return; }
+    if (dsum != ndel) job_error(J, 3, r);
     if (emit) O.finish(len);
     else {  // pbsim2noError.cpp:1711 prints mut.seq, the oriented template of length len'
 #pragma unroll 1

@@ -28,7 +28,7 @@ int main(int argc, char** argv) {
         else break;
     }
     if (a >= argc) {
-        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|pbsim|haplotype2reads> <argv of the reference's command>\n");
+        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|BuildReadLengthBins|Fastq2LengthHistogram|pbsim|haplotype2reads> <argv of the reference's command>\n");
         return 2;
     }
     const std::string cls = argv[a++];
@@ -124,6 +124,17 @@ int main(int argc, char** argv) {
         aa.input_files_list = args[0]; aa.min_distance = atoi(args[1]); aa.max_distance = atoi(args[2]);
         aa.reference_file = args[3]; aa.repeat_intervals_file = args[4]; aa.segdups_file = args[5];
         rc = sp_annotate_vcf(ctx, &aa);
+    } else if (cls == "BuildReadLengthBins") {
+        // INPUT_FILES_LIST BIN_LENGTH MAX_READ_LENGTH GENOME_LENGTH_HAPLOID OUTPUT_PREFIX (src/BuildReadLengthBins.java:21-27)
+        if (args.size() < 5) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
+        sp_build_bins_args ba;
+        ba.input_files_list = args[0]; ba.bin_length = atoi(args[1]); ba.max_read_length = atoi(args[2]);
+        ba.genome_length_haploid = atoll(args[3]); ba.output_prefix = args[4];
+        rc = sp_build_read_length_bins(ctx, &ba);
+    } else if (cls == "Fastq2LengthHistogram") {
+        // FASTQ_FILE BIN_LENGTH MAX_READ_LENGTH OUTPUT_FILE_HISTOGRAM OUTPUT_FILE_MAX (src/Fastq2LengthHistogram.java:11-16)
+        if (args.size() < 5) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
+        rc = sp_fastq2length_histogram(ctx, args[0], atoi(args[1]), atoi(args[2]), args[3], args[4]);
     } else if (cls == "haplotype2reads") {
         // docker/haplotype2reads.sh:16-24,31-32,53-64 for one individual, without the haplotype_<i>.fa files and the bucket:
         // ID1 LENGTH_MIN LENGTH_MAX LENGTH_MEAN LENGTH_STDEV MAX_COVERAGE REFERENCE_FILE HAPLOTYPE2VARIANTS_FILE VARIANTS_FILE

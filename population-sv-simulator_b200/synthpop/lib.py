@@ -101,6 +101,12 @@ class AnnotateArgs(C.Structure):
                 ("reference_file", C.c_char_p), ("repeat_intervals_file", C.c_char_p), ("segdups_file", C.c_char_p)]
 
 
+class BuildBinsArgs(C.Structure):
+    """sp_build_bins_args: positional argv of BuildReadLengthBins.main (src/BuildReadLengthBins.java:21-27)."""
+    _fields_ = [("input_files_list", C.c_char_p), ("bin_length", C.c_int32), ("max_read_length", C.c_int32),
+                ("genome_length_haploid", C.c_int64), ("output_prefix", C.c_char_p)]
+
+
 def load() -> C.CDLL:
     """dlopen the in-tree libsynthpop_cuda.so and declare every prototype of include/synthpop_cuda.h."""
     global _lib
@@ -131,6 +137,8 @@ def load() -> C.CDLL:
         "sp_reads_mix_timing": (C.c_int, [vp, vp, vp]),
         "sp_haplotype2reads": (C.c_int, [vp, i32, i64, cp, vp, vp]),
         "sp_haplotype_read_seed": (C.c_uint32, [C.c_uint32, i32]),
+        "sp_test_double_to_string": (C.c_int, [C.c_double, cp, i32]),
+        "sp_test_number_format4": (C.c_int, [C.c_double, cp, i32]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
         "sp_reference_length": (i64, [vp]),
@@ -177,6 +185,9 @@ def load() -> C.CDLL:
         "sp_annotate_load": (C.c_int, [vp, cp, cp, cp]),
         "sp_annotate_file": (C.c_int, [vp, cp, cp, i32, i32, P(i64)]),
         "sp_annotate_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double), P(i64)]),
+        "sp_build_read_length_bins": (C.c_int, [vp, P(BuildBinsArgs)]),
+        "sp_fastq2length_histogram": (C.c_int, [vp, cp, i32, i32, cp, cp]),
+        "sp_build_bins_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double), P(C.c_double), P(i64), P(i64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -565,6 +576,27 @@ class Context:
         a, b, n = C.c_double(), C.c_double(), C.c_int64()
         self._check(self.lib.sp_annotate_timing(self.h, C.byref(a), C.byref(b), C.byref(n)))
         return dict(load_s=a.value, kernel_ms=b.value, records=n.value)
+
+    # ---- §8(f) rank 3: BuildReadLengthBins / Fastq2LengthHistogram -----------------------------------------------------------
+    def build_read_length_bins(self, argv):
+        """BuildReadLengthBins.main(args) (src/BuildReadLengthBins.java:21-105): INPUT_FILES_LIST BIN_LENGTH MAX_READ_LENGTH
+        GENOME_LENGTH_HAPLOID OUTPUT_PREFIX."""
+        a = [str(x) for x in argv]
+        if len(a) < 5:
+            raise IndexError("BuildReadLengthBins takes 5 positional arguments")
+        args = BuildBinsArgs(a[0].encode(), int(a[1]), int(a[2]), int(a[3]), a[4].encode())
+        self._check(self.lib.sp_build_read_length_bins(self.h, C.byref(args)))
+
+    def fastq2length_histogram(self, argv):
+        """Fastq2LengthHistogram.main(args): FASTQ_FILE BIN_LENGTH MAX_READ_LENGTH OUTPUT_FILE_HISTOGRAM OUTPUT_FILE_MAX."""
+        a = [str(x) for x in argv]
+        self._check(self.lib.sp_fastq2length_histogram(self.h, a[0].encode(), int(a[1]), int(a[2]), a[3].encode(), a[4].encode()))
+
+    def build_bins_timing(self):
+        a, b, d = C.c_double(), C.c_double(), C.c_double()
+        n, nb = C.c_int64(), C.c_int64()
+        self._check(self.lib.sp_build_bins_timing(self.h, C.byref(a), C.byref(b), C.byref(d), C.byref(n), C.byref(nb)))
+        return dict(index_ms=a.value, shuffle_ms=b.value, copy_ms=d.value, records=n.value, bytes=nb.value)
 
     def length_bins_timing(self):
         a, b = C.c_double(), C.c_double()

@@ -67,28 +67,90 @@ def fmt(lib, fn, x):
     return buf.value.decode()
 
 
-def test_double_to_string(oracle_lib):
+def _formatters():
+    """(name, double->str for Double.toString, double->str for NumberFormat4): the oracle's copy and the product's copy
+    (csrc/api.cu) — the same vectors must hold for both, they are separate pieces of code."""
+    import oracle_helpers as oh
+    from synthpop import lib as splib
+    o, p = oh.load_oracle(), splib.load()
+    return [("oracle", lambda x: fmt(o, "oracle_double_to_string", x), lambda x: fmt(o, "oracle_number_format4", x)),
+            ("product", lambda x: fmt(p, "sp_test_double_to_string", x), lambda x: fmt(p, "sp_test_number_format4", x))]
+
+
+def java_layout(x: float) -> str:
+    """Double.toString's layout rules (Javadoc) applied to the shortest round-trip digits CPython's repr finds (David Gay's
+    dtoa, an implementation independent of both restatements): plain decimal for 1e-3 <= |x| < 1e7, else d.dddE[-]n; at
+    least one fractional digit."""
+    if x == 0:
+        return "-0.0" if str(x).startswith("-") else "0.0"
+    r = repr(abs(x))
+    if "e" in r:
+        mant, e = r.split("e")
+        exp = int(e)
+    else:
+        mant, exp = r, 0
+    ip, _, fp = mant.partition(".")
+    digits = (ip + fp).lstrip("0")
+    exp10 = exp + len(ip) - 1 if ip.strip("0") else exp - (len(fp) - len(fp.lstrip("0"))) - 1
+    digits = digits.rstrip("0") or "0"
+    if len(digits) == 1:   # at least two digits are shown: the two-digit decimal closest to x (4.9E-324, not 5.0E-324)
+        m2, e2 = f"{abs(x):.1e}".split("e")
+        digits, exp10 = m2.replace(".", "").rstrip("0") or "0", int(e2)
+    sign = "-" if x < 0 else ""
+    if 1e-3 <= abs(x) < 1e7:
+        if exp10 >= 0:
+            whole = (digits + "0" * (exp10 + 1))[: exp10 + 1]
+            frac = digits[exp10 + 1:] or "0"
+            return f"{sign}{whole}.{frac}"
+        return f"{sign}0.{'0' * (-exp10 - 1)}{digits}"
+    return f"{sign}{digits[0]}.{digits[1:] or '0'}E{exp10}"
+
+
+def test_double_to_string():
+    # known answers: the Javadoc's own examples and the published regression values of the JDK-19 rewrite (Raffaello Giulietti,
+    # JDK-4511638): boundaries of the plain/scientific switch, the largest, smallest normal and smallest subnormal doubles, a
+    # power of two whose shortest form older JDKs missed (2^-44), 1e23 (older JDKs printed 1.0E23 only by luck of their digit loop)
     cases = {0.05: "0.05", 1.0: "1.0", 5.0e-4: "5.0E-4", 1 / 6000: "1.6666666666666666E-4", 0.001: "0.001",
              9999999.0: "9999999.0", 1.0e7: "1.0E7", 0.3: "0.3", 2.0 / 3: "0.6666666666666666", 100.0: "100.0",
              1.0e-5: "1.0E-5", 123456.789: "123456.789", 4.9e-324: "4.9E-324", 0.0: "0.0", 12345678.9: "1.23456789E7",
-             0.1 + 0.2: "0.30000000000000004", 1.0e21: "1.0E21", 0.55: "0.55"}
-    for x, s in cases.items():
-        assert fmt(oracle_lib, "oracle_double_to_string", x) == s
-    # every value round-trips and is the shortest representation python's repr also finds
+             0.1 + 0.2: "0.30000000000000004", 1.0e21: "1.0E21", 0.55: "0.55",
+             2.0e-3: "0.002", float(np.nextafter(0.001, 0)): "9.999999999999998E-4", 9999999.999999998: "9999999.999999998",
+             1.0e23: "1.0E23", 1.7976931348623157e308: "1.7976931348623157E308",
+             2.2250738585072014e-308: "2.2250738585072014E-308", 2.0 ** -44: "5.684341886080802E-14", 2.0e-322: "2.0E-322",
+             8.41e21: "8.41E21", 2.82879384806159e17: "2.82879384806159E17", 1.387364135037754e18: "1.387364135037754E18",
+             1.45800632428665e17: "1.45800632428665E17", 123456789.0: "1.23456789E8", -0.25: "-0.25", -1.0e-10: "-1.0E-10"}
     rng = np.random.default_rng(1)
-    for x in np.concatenate([rng.random(2000), rng.random(500) * 1e-4, (np.arange(1, 400) / 400.0)]):
-        s = fmt(oracle_lib, "oracle_double_to_string", float(x))
-        assert float(s.replace("E", "e")) == float(x)
-        mant = s.split("E")[0].replace(".", "").replace("-", "").strip("0")
-        assert mant == repr(float(x)).split("e")[0].replace(".", "").replace("-", "").strip("0")
+    randoms = np.concatenate([rng.random(2000), rng.random(500) * 1e-4, (np.arange(1, 400) / 400.0),
+                              np.exp(rng.uniform(-700, 700, size=1500)), np.ldexp(rng.random(300), rng.integers(-1070, -1020, size=300))])
+    for name, d2s, _ in _formatters():
+        for x, s in cases.items():
+            assert d2s(x) == s, (name, x)
+            assert java_layout(x) == s, x   # the layout helper below agrees with the published strings
+        for x in randoms:
+            x = float(x)
+            s = d2s(x)
+            assert float(s.replace("E", "e")) == x, (name, x)
+            assert s == java_layout(x), (name, x)
 
 
-def test_number_format4(oracle_lib):
+def test_number_format4():
     cases = {0.0: "0.0000", 1.0: "1.0000", 0.03125: "0.0312", 0.09375: "0.0938", 0.12345: "0.1235", 0.5: "0.5000",
              1234.5: "1,234.5000", 1234567.891: "1,234,567.8910", -0.25: "-0.2500", -1234.56789: "-1,234.5679",
-             0.00005: "0.0001", 2.5e-5: "0.0000", 999.99995: "1,000.0000"}
-    for x, s in cases.items():
-        assert fmt(oracle_lib, "oracle_number_format4", x) == s, x
+             0.00005: "0.0001", 2.5e-5: "0.0000", 999.99995: "1,000.0000", 0.00015: "0.0001", 0.00025: "0.0003",
+             1e9 + 0.5: "1,000,000,000.5000"}
+    import decimal
+    rng = np.random.default_rng(3)
+    randoms = np.concatenate([rng.random(500), rng.random(300) * 5000 - 2500, rng.integers(0, 20000, size=300) / 20000.0])
+    for name, _, nf4 in _formatters():
+        for x, s in cases.items():
+            assert nf4(x) == s, (name, x)
+        for x in randoms:   # HALF_EVEN on the exact binary value, grouping by thousands: python's decimal does the same from the exact value
+            x = float(x)
+            q = decimal.Decimal(x).quantize(decimal.Decimal("0.0001"), rounding=decimal.ROUND_HALF_EVEN)
+            want = f"{q:,.4f}"
+            if want.startswith("-") and float(q) == 0:
+                want = "-" + want[1:]   # NumberFormat prints "-0.0000" for a negative value that rounds to zero
+            assert nf4(x) == want, (name, x)
 
 
 def test_binary_search(oracle_lib):
