@@ -468,6 +468,64 @@ def file_emission_leg(splib, synth, work, local_rank):
             "print_haplotypes_s": round(t_print, 3), "fasta_bytes": fa_bytes, "print_haplotypes_MBps": fa_bytes / t_print / 1e6}
 
 
+def next_rows_leg(splib, synth, work, local_rank, emission_dir, cpu_baseline=True):
+    """The rows either side of the path on the same box: AnnotateVCF over the truth VCFs
+    the file-emission leg wrote, BuildReadLengthBins over a synthetic CCS-like FASTQ. Wall seconds through the C ABI with files
+    on local disk, the device share beside them, the CPU restatement timed on the same inputs."""
+    import oracle_helpers as oh
+    oh.ensure_oracle_built()
+    oracle = os.path.join(ROOT, "oracle", "_build", "synthpop_oracle")
+    out = {}
+    inp_dir = os.path.join(work, "c1_in")
+    vcfs = sorted(os.path.join(emission_dir, f) for f in os.listdir(emission_dir) if f.endswith(".vcf") and "_annotated" not in f)
+    lst = os.path.join(work, "annot_list.txt")
+    open(lst, "w").write("".join(v + "\n" for v in vcfs))
+    argv = [lst, "10", "100", os.path.join(inp_dir, "reference.fa"), os.path.join(inp_dir, "repeatIntervals.txt"), os.path.join(inp_dir, "segdups.txt")]
+    with splib.Context(local_rank, 42) as ctx:
+        t0 = time.perf_counter()
+        ctx.annotate_vcf(argv)
+        t = time.perf_counter() - t0
+        tm = ctx.annotate_timing()
+    nbytes = sum(os.path.getsize(v) for v in vcfs)
+    out["annotate_vcf"] = {"workload": f"AnnotateVCF over the {len(vcfs)} truth VCFs of configs[0] ({nbytes} bytes), chr21-sized reference",
+                           "wall_s": round(t, 3), "load_positions_s": round(tm["load_s"], 3), "records": tm["records"],
+                           "records_per_s": tm["records"] / max(t - tm["load_s"], 1e-9), "last_file_kernel_ms": tm["kernel_ms"]}
+    if cpu_baseline:
+        t0 = time.perf_counter()
+        subprocess.run([oracle, "AnnotateVCF"] + argv, check=True, stderr=subprocess.DEVNULL)
+        out["annotate_vcf"]["cpu_port_wall_s"] = round(time.perf_counter() - t0, 3)
+    # BuildReadLengthBins: 60 000 records around two modes, sequence + quality from a random pool
+    rng = np.random.default_rng(11)
+    pool = np.frombuffer(b"ACGT", np.uint8)[rng.integers(0, 4, size=1 << 22, dtype=np.uint8)].tobytes()
+    qual = rng.integers(33 + 20, 33 + 60, size=1 << 22).astype(np.uint8).tobytes()
+    fq = os.path.join(work, "bins_in.fastq")
+    n_rec = 60_000
+    with open(fq, "wb") as f:
+        for k in range(n_rec):
+            ln = max(50, int(rng.normal(9000, 1500) if rng.random() < 0.3 else rng.normal(15000, 2000)))
+            a = int(rng.integers(0, (1 << 22) - ln))
+            f.write(b"@m64/%d/ccs\n" % k + pool[a:a + ln] + b"\n+\n" + qual[a:a + ln] + b"\n")
+    lst2 = os.path.join(work, "bins_list.txt")
+    open(lst2, "w").write(fq + "\n")
+    argv = [lst2, "500", "35000", "3100000000", os.path.join(work, "bb_")]
+    with splib.Context(local_rank, 42) as ctx:
+        ctx.build_read_length_bins(argv)   # warm-up (allocations)
+        t0 = time.perf_counter()
+        ctx.build_read_length_bins(argv)
+        t = time.perf_counter() - t0
+        tm = ctx.build_bins_timing()
+    fq_bytes = os.path.getsize(fq)
+    out["build_read_length_bins"] = {"workload": f"BuildReadLengthBins, {n_rec} records, {fq_bytes} bytes of FASTQ, 70 bins of 500 bp",
+                                     "wall_s": round(t, 3), "fastq_MBps_wall": fq_bytes / t / 1e6, "device_ms": {k: round(tm[k], 3) for k in ("index_ms", "shuffle_ms", "copy_ms")},
+                                     "gather_GBps_algorithmic": 2.0 * tm["bytes"] / max(tm["copy_ms"], 1e-9) / 1e6}
+    if cpu_baseline:
+        argv_o = argv[:4] + [os.path.join(work, "bbo_")]
+        t0 = time.perf_counter()
+        subprocess.run([oracle, "--seed", "42", "BuildReadLengthBins"] + argv_o, check=True, stderr=subprocess.DEVNULL)
+        out["build_read_length_bins"]["cpu_port_wall_s"] = round(time.perf_counter() - t0, 3)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -706,9 +764,10 @@ def main():
     if dist is not None:
         dist.all_reduce(e2e_val, op=dist.ReduceOp.SUM)
 
-    emission = None
+    emission = next_rows = None
     if args.file_emission and rank == 0 and world == 1:
         emission = file_emission_leg(splib, synth, work, local_rank)
+        next_rows = next_rows_leg(splib, synth, work, local_rank, os.path.join(work, "c1_out"), cpu_baseline=not args.no_cpu_baseline)
 
     if rank == 0:
         peak, peak_kind = measured_peak_gbs()
@@ -759,6 +818,8 @@ def main():
             line["trio"] = trio_obj
         if emission is not None:
             line["file_emission"] = emission
+        if next_rows is not None:
+            line["next_rows"] = next_rows
         if world == 1 and not args.no_cpu_baseline:
             if reads_obj is not None:
                 rb = reads_cpu_baseline(synth, work)

@@ -49,6 +49,10 @@ int64_t sp_kernel_launches(const sp_ctx* ctx);
  * Return the string length. */
 int sp_test_double_to_string(double x, char* out, int32_t capacity);
 int sp_test_number_format4(double x, char* out, int32_t capacity);
+/* Bandwidth probes behind the design of the tiled copy kernel (csrc/probe.cu, tools/probe_copy_variants.py): n_slots slots of
+ * slot_bytes filled region-major from one shared source shifted by `misalign` bytes. kind 0 = stores only, 1 = the register
+ * path of materialise_kernel, 2 = cp.async.bulk into shared memory under an mbarrier. Device milliseconds per launch. */
+int sp_probe_bandwidth(sp_ctx* ctx, int32_t kind, int64_t slot_bytes, int32_t n_slots, int32_t misalign, int32_t reps, double* ms_per_launch);
 
 /* ---- row A1: reference ------------------------------------------------------------------------------ */
 /* SimulateHaplotypes.loadReference(String) (src/SimulateHaplotypes.java:119-134): skip one header line, trim and

@@ -132,18 +132,39 @@ static void set_reference(sp_ctx* c) {
     c->plan_last = -1; c->plan_first = 0;
 }
 
-// SimulateHaplotypes.loadReference, src/SimulateHaplotypes.java:119-134
+// SimulateHaplotypes.loadReference, src/SimulateHaplotypes.java:119-134: skip one header line, String.trim() every
+// following line and concatenate. Lines are found with memchr and copied with memcpy (a chr1-sized FASTA is four million
+// 60-byte lines; this loop is most of row A1's time).
 void load_reference_fasta(sp_ctx* c, const char* path) {
     std::vector<char> buf = slurp(path);
-    Lines lines(buf.data(), buf.data() + buf.size());
+    const char* p = buf.data();
+    const char* const end = p + buf.size();
+    auto next_line = [&](const char*& b, const char*& e) -> bool {   // BufferedReader.readLine: \n, \r or \r\n end a line
+        if (p >= end) return false;
+        b = p;
+        const char* q = (const char*)memchr(p, '\n', (size_t)(end - p));
+        const char* stop = q ? q : end;
+        const char* r = (const char*)memchr(p, '\r', (size_t)(stop - p));
+        if (r) {   // a carriage return before the line feed: the line ends there ("\r\n" counts as one terminator)
+            e = r;
+            p = (r + 1 < end && r[1] == '\n') ? r + 2 : r + 1;
+        } else {
+            e = stop;
+            p = q ? q + 1 : end;
+        }
+        return true;
+    };
     const char *b, *e;
-    lines.next(b, e);  // Skipping header
+    next_line(b, e);  // Skipping header
     c->h_ref.clear();
-    c->h_ref.reserve(buf.size());
-    while (lines.next(b, e)) {
-        trim_span(b, e);
-        c->h_ref.insert(c->h_ref.end(), (const uint8_t*)b, (const uint8_t*)e);
+    c->h_ref.resize(buf.size());
+    uint8_t* out = c->h_ref.data();
+    while (next_line(b, e)) {
+        if (b < e && ((unsigned char)*b <= ' ' || (unsigned char)e[-1] <= ' ')) trim_span(b, e);
+        memcpy(out, b, (size_t)(e - b));
+        out += e - b;
     }
+    c->h_ref.resize((size_t)(out - c->h_ref.data()));
     if (c->h_ref.size() > (size_t)INT32_MAX) throw Error(SP_ERR_ARG, "reference longer than 2^31-1 (the reference uses int coordinates)");
     set_reference(c);
 }
@@ -262,7 +283,10 @@ void FileSink::write_file(const std::string& path, const uint8_t* d_src, int64_t
         {
             std::unique_lock<std::mutex> g(m_);
             cv_.wait(g, [&] { return !slots_[(size_t)next_].busy; });
-            if (failed_) throw Error(SP_ERR_JAVA_EXCEPTION, error_);
+            if (failed_) {   // drain() reports it: nothing more is queued for this file
+                g.unlock();
+                drain();
+            }
             slot = next_; next_ = (next_ + 1) % (int)slots_.size();
             slots_[(size_t)slot].busy = true; pending_++;
         }
@@ -281,10 +305,23 @@ void FileSink::write_file(const std::string& path, const uint8_t* d_src, int64_t
 void FileSink::drain() {
     std::unique_lock<std::mutex> g(m_);
     cv_.wait(g, [&] { return pending_ == 0; });
-    if (failed_) throw Error(SP_ERR_JAVA_EXCEPTION, error_);
+    if (failed_) {   // report once; the sink stays usable for the next file
+        failed_ = false;
+        const std::string what = error_;
+        throw Error(SP_ERR_JAVA_EXCEPTION, what);
+    }
 }
 
 void FileSink::finish() { drain(); }
+
+FileSink& file_sink(sp_ctx* c) {
+    if (!c->sink) c->sink = new FileSink(c->device, 4, 32ll << 20);
+    return *c->sink;
+}
+void free_file_sink(sp_ctx* c) {
+    delete c->sink;
+    c->sink = nullptr;
+}
 
 static void check_planned(sp_ctx* c, int32_t h) {
     if (c->plan_last < c->plan_first || h < c->plan_first || h > c->plan_last)
@@ -340,6 +377,7 @@ void sp_destroy(sp_ctx* ctx) {
     sp::free_length_bins(ctx);
     sp::free_read_mix(ctx);
     sp::free_annotate(ctx);
+    sp::free_file_sink(ctx);
     if (ctx->ev_planned) cudaEventDestroy(ctx->ev_planned);
     for (auto& b : ctx->plan_set) if (b.ev_used) cudaEventDestroy(b.ev_used);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
@@ -529,7 +567,7 @@ int sp_print_haplotypes(sp_ctx* ctx, int32_t first, int32_t last, const char* re
     int32_t batch = (int32_t)std::max<int64_t>(1, std::min<int64_t>(64, (int64_t)(free_b / 2) / std::max<int64_t>(per_hap, 1)));
     // Device -> pinned ring -> files: the copy engine fills chunk k+1 (and the copy kernel materialises the next batch)
     // while a writer thread pushes chunk k into the page cache.
-    sp::FileSink sink(ctx->device, 6, 32ll << 20);
+    sp::FileSink& sink = sp::file_sink(ctx);
     for (int32_t a = first; a <= last; a += batch) {
         const int32_t b = std::min(last, a + batch - 1);
         sink.drain();   // the slots are about to be overwritten: every copy out of them must have been issued AND done

@@ -16,6 +16,7 @@ struct ReadState;
 struct LengthBinState;
 struct ReadMixState;
 struct AnnotateState;
+class FileSink;
 struct LengthBinBuilderState;
 
 struct Error : std::runtime_error {
@@ -69,25 +70,19 @@ constexpr int64_t SEG_OFF_MASK = (int64_t(1) << 48) - 1;
 
 constexpr int TILE_BYTES = 16384;  // output bytes per CTA tile of the materialisation kernel
 
-// Per-tile descriptor written by tile_table_kernel. nseg == 0: the tile lies inside one forward segment and srcw holds
-// its kind (bits 62..60) and the source byte offset of the tile's first byte; otherwise segments [s0, s0+nseg) of the
-// slot intersect the tile.
+// The copy kernel works on RUNS: maximal pieces of one segment inside one 16 KiB output tile. A run is a plain copy
+// (one source pointer, one length), so a tile needs no segment table, no search and no barrier: its descriptor holds the
+// first run (offset 0 of the tile) and says where the tile's other runs, if any, sit in the run array. Built per launch by
+// tile_count_kernel + a scan + tile_fill_kernel.
 struct alignas(16) TileDesc {
-    int64_t srcw;
-    int32_t s0, nseg;
+    int64_t srcw0;        // first run: kind (bits 62..60) + source byte offset of the tile's first byte (SEG_PAD: nothing to copy)
+    uint32_t len0_more;   // bits 0..14: length of the first run (0..16384), bits 15..31: number of further runs
+    int32_t item_first;   // index of the tile's second run in the run array
 };
-// Optional inline segment table of a tile with at most INLINE_SEGS segments (the record-gather uses of the copy kernel:
-// read mix, length bins): entry i of tile t lives at ((SegEntry*)(desc + ntiles))[t * INLINE_SEGS + i], so the copy kernel
-// can load it together with the descriptor instead of chasing seg_dst/seg_src afterwards. rel = first output byte of the
-// segment minus the tile's first byte (clamped to +-2^30), adj = source offset that corresponds to the tile's first byte.
-// A general tile whose entries were written has bit 40 of srcw set and rel of the segment after its last one in the low
-// 32 bits of srcw.
-struct alignas(16) SegEntry {
-    int32_t rel, kind;
-    int64_t adj;
+struct alignas(16) RunItem {
+    int64_t srcw;         // kind + source offset of the run's first output byte (reverse-complemented runs walk downwards from it)
+    int32_t off, len;     // output bytes [off, off+len) of the tile
 };
-constexpr int INLINE_SEGS = 8;
-constexpr int64_t TILE_INLINE_FLAG = int64_t(1) << 40;
 
 }  // namespace sp
 
@@ -146,11 +141,17 @@ struct sp_ctx {
     struct PlanSet {   // everything sp_materialise reads besides the reference, the payloads and the slots
         sp::DevBuf<int64_t> seg_dst, seg_src, seg_base, aux_off;
         sp::DevBuf<sp::TileDesc> tile_desc;
+        sp::DevBuf<sp::RunItem> items;
         sp::DevBuf<uint8_t> aux;
         cudaEvent_t ev_used = nullptr;   // recorded on the materialisation stream after the last copy kernel that read this set
     } plan_set[2];
     int plan_cur = 0;
     sp::DevBuf<int64_t> d_hap_len;
+    // run tables of the record-gather uses of the copy kernel (launch_tiled_copy) and scratch of the table builders
+    sp::DevBuf<sp::TileDesc> d_copy_desc;
+    sp::DevBuf<sp::RunItem> d_copy_items;
+    sp::DevBuf<int32_t> d_tile_more, d_tile_s0, d_tile_scan;
+    sp::DevBuf<uint8_t> d_tile_tmp;
     int64_t* h_pinned = nullptr;         // small pinned staging area for the size read-backs (plan, rows G/C/N)
     size_t h_pinned_bytes = 0;
     int64_t* pinned(size_t bytes) {
@@ -186,6 +187,9 @@ struct sp_ctx {
     // gather copy), records and bytes written
     double bb_ms[3] = {0.0, 0.0, 0.0};
     int64_t bb_records = 0, bb_bytes = 0;
+
+    // device -> pinned ring -> files, created on first use and kept (pinning 128 MB costs tens of milliseconds)
+    sp::FileSink* sink = nullptr;
 };
 
 // Entry/exit of every extern "C" function: bind the context's device (failing loudly), turn exceptions into codes.

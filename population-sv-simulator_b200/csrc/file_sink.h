@@ -37,4 +37,8 @@ private:
     std::string error_;
 };
 
+// The context's sink (4 chunks of 32 MiB), created on first use.
+FileSink& file_sink(sp_ctx* c);
+void free_file_sink(sp_ctx* c);
+
 }  // namespace sp

@@ -30,8 +30,7 @@
 namespace sp {
 
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
-                       int n_slots);
+                       const int64_t* seg_src, const int64_t* seg_base, int64_t n_segments, uint8_t* out, int64_t stride, int n_slots);
 
 namespace {
 
@@ -389,7 +388,6 @@ void build_read_length_bins(sp_ctx* c, const sp_build_bins_args* a) {
     DevBuf<unsigned long long> d_hist;
     DevBuf<uint64_t> d_key, d_key2;
     DevBuf<uint8_t> d_tmp, d_out;
-    DevBuf<TileDesc> d_desc;
     d_rec_start.reserve(R1); d_rec_bytes.reserve(R1); d_bin.reserve(R1); d_bin2.reserve(R1); d_idx.reserve(R1); d_order.reserve(R1);
     d_hist.reserve(2 * NB1); d_flag.reserve(2);
     SP_CUDA(cudaMemsetAsync(d_hist.p, 0, 2 * NB1 * 8, st));
@@ -510,11 +508,10 @@ void build_read_length_bins(sp_ctx* c, const sp_build_bins_args* a) {
     const int64_t total = h_bin_byte[(size_t)n_bins];
     const int64_t stride = std::max<int64_t>(TILE_BYTES, (total + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES);
     d_out.reserve((size_t)stride, 0.0);
-    d_desc.reserve((size_t)(stride / TILE_BYTES) * (1 + INLINE_SEGS));
-    launch_tiled_copy(c, I.d_blob.p, I.d_blob.p, I.d_blob.p, d_seg_dst.p, d_seg_src.p, d_seg_base.p, d_desc.p, d_out.p, stride, 1);
+    launch_tiled_copy(c, I.d_blob.p, I.d_blob.p, I.d_blob.p, d_seg_dst.p, d_seg_src.p, d_seg_base.p, R + 2, d_out.p, stride, 1);
     SP_CUDA(cudaEventRecord(ev[3], st));
     {
-        FileSink sink(c->device, 4, 32ll << 20);
+        FileSink& sink = file_sink(c);
         for (int32_t b = 0; b < n_bins; b++)
             sink.write_file(prefix + std::to_string(b) + ".bin", d_out.p + h_bin_byte[(size_t)b], h_bin_byte[(size_t)b + 1] - h_bin_byte[(size_t)b], st);
         sink.finish();

@@ -23,8 +23,7 @@
 namespace sp {
 
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
-                       int n_slots);
+                       const int64_t* seg_src, const int64_t* seg_base, int64_t n_segments, uint8_t* out, int64_t stride, int n_slots);
 
 constexpr int LB_CTA = 256;  // attempts per CTA
 
@@ -43,7 +42,6 @@ struct LengthBinState {
     DevBuf<int32_t> d_bin, d_rec, d_hist_blocks, d_hist;
     DevBuf<int64_t> d_block_sums, d_acc_incl, d_cov_incl, d_bytes_excl, d_result;
     DevBuf<int64_t> d_seg_dst, d_seg_src, d_seg_base;
-    DevBuf<TileDesc> d_tile_first;
     DevBuf<uint8_t> d_hdr, d_out;
     int64_t n_reads = 0, out_bytes = 0, attempts = 0, coverage = 0;
     std::vector<int32_t> h_hist;
@@ -412,7 +410,6 @@ static int sample_bins(sp_ctx* c, const double* cdf, int32_t n_bins, int64_t tar
     const int64_t stride = (B.out_bytes + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES;
     B.d_seg_dst.reserve(nseg); B.d_seg_src.reserve(nseg); B.d_seg_base.reserve(2);
     B.d_hdr.reserve((size_t)header_bytes_before(B.n_reads) + 64);
-    B.d_tile_first.reserve((stride / TILE_BYTES) * (1 + INLINE_SEGS));  // descriptors + inline segment entries
     B.d_out.reserve((size_t)stride, 0.02);
     const int64_t seg_base[2] = {0, nseg};
     SP_CUDA(cudaMemcpyAsync(B.d_seg_base.p, seg_base, sizeof seg_base, cudaMemcpyHostToDevice, st));
@@ -423,7 +420,7 @@ static int sample_bins(sp_ctx* c, const double* cdf, int32_t n_bins, int64_t tar
     c->launches++;
     SP_CUDA(cudaGetLastError());
     SP_CUDA(cudaEventRecord(B.ev1, st));
-    launch_tiled_copy(c, B.d_blob.p, B.d_blob.p, B.d_hdr.p, B.d_seg_dst.p, B.d_seg_src.p, B.d_seg_base.p, B.d_tile_first.p, B.d_out.p, stride, 1);
+    launch_tiled_copy(c, B.d_blob.p, B.d_blob.p, B.d_hdr.p, B.d_seg_dst.p, B.d_seg_src.p, B.d_seg_base.p, nseg, B.d_out.p, stride, 1);
     SP_CUDA(cudaEventRecord(B.ev2, st));
     SP_CUDA(cudaMemcpyAsync(B.h_hist.data(), B.d_hist.p, n_bins * 4, cudaMemcpyDeviceToHost, st));
     SP_CUDA(cudaStreamSynchronize(st));

@@ -4,14 +4,18 @@
 //   plan_kernel ......... one CTA per haplotype; every edit of the sorted edit list becomes three segment
 //                         slots (reference gap, body, second DUP copy) and a block-wide exclusive scan over the
 //                         per-edit output deltas yields each segment's destination offset (the "segmented scan").
-//   tile_table_kernel ... one thread per 16 KiB output tile: index of the first segment that intersects it.
+//   tile_count/fill ..... one thread per 16 KiB output tile: the tile's RUNS (pieces of one segment inside the tile),
+//                         the first one in the 16-byte tile descriptor, the others in a run array (count, scan, fill).
 //   materialise_kernel .. one CTA per output tile, tiles ordered region-major across the haplotypes of the
-//                         batch so that the reference window they share stays in the 126 MB L2; 16-byte
-//                         aligned streaming stores; the arbitrary byte shift between source and destination
-//                         is resolved in registers (two aligned 16-byte loads + funnel shifts).
+//                         batch so that the reference window they share stays in the 126 MB L2. A run is a plain
+//                         copy: 16-byte aligned streaming stores, the arbitrary byte shift between source and
+//                         destination resolved in registers (two aligned 16-byte loads + funnel shifts), a few byte
+//                         stores at the ends of a run that does not start or end on a 16-byte boundary. No segment
+//                         table, no search, no barrier in the copy kernel.
 //
 // HBM-bound: 1 B read + 1 B written per output base (2 B/bp algorithmic).
 #include "common.cuh"
+#include <cub/device/device_scan.cuh>
 
 namespace sp {
 
@@ -138,56 +142,61 @@ plan_kernel(const int8_t* __restrict__ type, const int32_t* __restrict__ pos, co
     }
 }
 
-// One thread per 16 KiB output tile: which segments intersect it, and — for the common tile that lies inside one
-// forward segment — where its source bytes start, so that the copy kernel needs ONE 16-byte descriptor load before its
-// data loads instead of a chain through tile_first -> seg_dst/seg_src.
+// One thread per 16 KiB output tile: the runs of the tile = the non-empty, non-PAD intersections of the slot's segments
+// with the tile, in output order. Pass 1 counts them (and remembers the first segment), a scan assigns each tile its
+// place in the run array, pass 2 writes the descriptor (first run) and the run array (the others).
+__device__ __forceinline__ int32_t first_segment_of_tile(const int64_t* __restrict__ seg_dst, int64_t n, int64_t x) {
+    int64_t lo = 0, hi = n;   // first local index with dst > x
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (seg_dst[mid] <= x) lo = mid + 1; else hi = mid;
+    }
+    return (int32_t)(lo - 1);
+}
+
+template <bool FILL>
 __global__ void __launch_bounds__(256)
-tile_table_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
-                  int n_hap, int64_t tiles_per_slot, TileDesc* __restrict__ desc, int inline_entries) {
+tile_runs_kernel(const int64_t* __restrict__ seg_dst, const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
+                 int n_hap, int64_t tiles_per_slot, int32_t* __restrict__ s0_io, int32_t* __restrict__ more, const int32_t* __restrict__ first_more,
+                 TileDesc* __restrict__ desc, RunItem* __restrict__ items) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= tiles_per_slot * n_hap) return;
     const int hb = (int)(idx / tiles_per_slot);
     const int64_t x = (idx % tiles_per_slot) * TILE_BYTES;
     const int64_t sb = seg_base[hb];
-    const int64_t n = seg_base[hb + 1] - sb;  // includes the PAD segment and the INT64_MAX sentinel
-    int64_t lo = 0, hi = n;                   // first local index with dst > x
-    while (lo < hi) {
-        const int64_t mid = (lo + hi) >> 1;
-        if (seg_dst[sb + mid] <= x) lo = mid + 1; else hi = mid;
-    }
-    const int64_t s0 = lo - 1;
-    int64_t lo2 = lo, hi2 = n;                // first local index with dst >= x + TILE_BYTES (the sentinel at the latest)
-    while (lo2 < hi2) {
-        const int64_t mid = (lo2 + hi2) >> 1;
-        if (seg_dst[sb + mid] < x + TILE_BYTES) lo2 = mid + 1; else hi2 = mid;
-    }
-    const int64_t s1 = lo2 - 1;
-    const int64_t src = seg_src[sb + s0];
-    const int kind = (int)(src >> SEG_KIND_SHIFT);
+    const int64_t* gd = seg_dst + sb;
+    const int64_t* gs = seg_src + sb;
+    const int32_t s0 = FILL ? s0_io[idx] : first_segment_of_tile(gd, seg_base[hb + 1] - sb, x);  // the sentinel (INT64_MAX) is never <= x
+    int32_t n_runs = 0;
     TileDesc d;
-    d.s0 = (int32_t)s0;
-    if (s1 == s0 && kind != SEG_REF_RC) {
-        d.nseg = 0;  // uniform tile
-        d.srcw = (int64_t(kind) << SEG_KIND_SHIFT) | (((src & SEG_OFF_MASK) + (x - seg_dst[sb + s0])) & SEG_OFF_MASK);
-    } else {
-        d.nseg = (int32_t)(s1 - s0 + 1);
-        d.srcw = 0;
-        if (inline_entries && d.nseg <= INLINE_SEGS) {
-            auto clamp = [](int64_t r) { return (int32_t)(r < -(1 << 30) ? -(1 << 30) : (r > (1 << 30) ? (1 << 30) : r)); };
-            SegEntry* e = (SegEntry*)(desc + tiles_per_slot * n_hap) + idx * INLINE_SEGS;
-            for (int i = 0; i < d.nseg; i++) {
-                const int64_t r = seg_dst[sb + s0 + i] - x;
-                const int64_t sw = seg_src[sb + s0 + i];
-                const int k = (int)(sw >> SEG_KIND_SHIFT);
-                SegEntry v;
-                v.rel = clamp(r); v.kind = k;
-                v.adj = k == SEG_REF_RC ? (sw & SEG_OFF_MASK) + r : (sw & SEG_OFF_MASK) - r;
-                e[i] = v;
+    d.srcw0 = int64_t(SEG_PAD) << SEG_KIND_SHIFT; d.len0_more = 0; d.item_first = 0;
+    int32_t at = FILL ? first_more[idx] : 0;
+    int64_t cur = gd[s0];
+    for (int32_t s = s0; cur < x + TILE_BYTES; s++) {
+        const int64_t nxt = gd[s + 1];
+        const int64_t a = cur > x ? cur : x, b = nxt < x + TILE_BYTES ? nxt : x + TILE_BYTES;
+        const int64_t sw = gs[s];
+        const int kind = (int)(sw >> SEG_KIND_SHIFT);
+        if (b > a && kind != SEG_PAD) {
+            if (FILL) {
+                const int64_t r = a - cur, o = sw & SEG_OFF_MASK;
+                const int64_t srcw = (int64_t(kind) << SEG_KIND_SHIFT) | ((kind == SEG_REF_RC ? o - r : o + r) & SEG_OFF_MASK);
+                if (n_runs == 0) {
+                    if (a == x) { d.srcw0 = srcw; d.len0_more = (uint32_t)(b - a); }
+                    else { RunItem it; it.srcw = srcw; it.off = (int32_t)(a - x); it.len = (int32_t)(b - a); items[at++] = it; }
+                } else { RunItem it; it.srcw = srcw; it.off = (int32_t)(a - x); it.len = (int32_t)(b - a); items[at++] = it; }
             }
-            d.srcw = TILE_INLINE_FLAG | (int64_t)(uint32_t)clamp(seg_dst[sb + s0 + d.nseg] - x);
+            // a first run that does not start at the tile's first byte goes to the run array too (the descriptor's run is empty)
+            n_runs += (n_runs == 0 && a != x) ? 2 : 1;
         }
+        cur = nxt;
     }
-    desc[idx] = d;
+    const int32_t n_more = n_runs > 0 ? n_runs - 1 : 0;
+    if (FILL) {
+        d.len0_more |= (uint32_t)n_more << 15;
+        d.item_first = first_more[idx];
+        desc[idx] = d;
+    } else { s0_io[idx] = s0; more[idx] = n_more; }
 }
 
 __device__ __forceinline__ uint4 shift_combine(uint4 A, uint4 B, unsigned m) {
@@ -203,73 +212,63 @@ __device__ __forceinline__ uint4 shift_combine(uint4 A, uint4 B, unsigned m) {
                       __funnelshift_r(x3, x4, s));
 }
 
-constexpr int MAX_TILE_SEGS = 96;
-constexpr int COUNT_SEARCH_SEGS = 12;  // up to here the segment of a chunk is found by counting (independent loads)
-
-// Tile with more than MAX_TILE_SEGS segments (thousands of tiny records): rare, kept simple. One 16-byte chunk at a
-// time, segment found by binary search in global memory, bytes gathered one by one.
-__device__ __noinline__ void copy_tile_many_segments(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload,
-                                                     const uint8_t* __restrict__ aux, const int64_t* __restrict__ gd,
-                                                     const int64_t* __restrict__ gs, int nseg, int64_t x0,
-                                                     uint8_t* __restrict__ dst_tile) {
-    for (int c = threadIdx.x; c < TILE_BYTES / 16; c += 256) {
-        const int64_t x = x0 + (int64_t)c * 16;
-        int i = 0, hi = nseg;  // last i in [0,nseg) with gd[i] <= x
-        while (hi - i > 1) {
-            const int mid = (i + hi) >> 1;
-            if (gd[mid] <= x) i = mid; else hi = mid;
+// One run: output bytes [a, a+n) of the tile from one source. Every thread of the CTA takes part.
+__device__ __forceinline__ void copy_run(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload, const uint8_t* __restrict__ aux,
+                                         int64_t srcw, int32_t a, int32_t n, uint8_t* __restrict__ dst_tile) {
+    const int kind = (int)(srcw >> SEG_KIND_SHIFT);
+    if (kind == SEG_PAD || n <= 0) return;
+    const int tid = threadIdx.x;
+    uint8_t* d = dst_tile + a;
+    if (kind == SEG_REF_RC) {   // an inversion (2 per thousand variants): byte by byte, walking the reference downwards
+        const uint8_t* sp = ref + (srcw & SEG_OFF_MASK);
+        for (int32_t i = tid; i < n; i += 256) d[i] = complement_base(__ldg(sp - i));
+        return;
+    }
+    const uint8_t* p = (kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux)) + (srcw & SEG_OFF_MASK);
+    const int32_t head = min(n, (16 - (a & 15)) & 15);   // bytes up to the first 16-byte boundary of the output (tiles are 16 KiB aligned)
+    const int32_t nbody = (n - head) >> 4, tail = (n - head) & 15;
+    if (tid < head) d[tid] = __ldg(p + tid);
+    if (tid >= 32 && tid - 32 < tail) d[head + nbody * 16 + (tid - 32)] = __ldg(p + head + nbody * 16 + (tid - 32));
+    const uint8_t* pb = p + head;
+    const unsigned m = (unsigned)((uintptr_t)pb & 15u);
+    const uint4* q = (const uint4*)(pb - m);
+    uint4* o = (uint4*)(d + head);
+    for (int32_t c0 = 0; c0 < nbody; c0 += 1024) {   // all loads of a batch before its stores: 8 in flight per thread
+        uint4 A[4], B[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int32_t c = c0 + u * 256 + tid;
+            if (c < nbody) { A[u] = __ldg(q + c); if (m) B[u] = __ldg(q + c + 1); }   // buffers carry >= 32 bytes of slack past their end
         }
-        int64_t dcur = gd[i], dnext = gd[i + 1], src = gs[i];
-        uint32_t w[4] = {0, 0, 0, 0};
-        bool any = false;
-#pragma unroll 1
-        for (int j = 0; j < 16; j++) {
-            const int64_t xb = x + j;
-            while (xb >= dnext) { i++; dcur = dnext; dnext = gd[i + 1]; src = gs[i]; }
-            const int kind = (int)(src >> SEG_KIND_SHIFT);
-            const int64_t o = src & SEG_OFF_MASK, r = xb - dcur;
-            uint8_t byte = 0;
-            if (kind == SEG_REF_FWD) byte = ref[o + r];
-            else if (kind == SEG_REF_RC) byte = complement_base(ref[o - r]);
-            else if (kind == SEG_PAYLOAD) byte = payload[o + r];
-            else if (kind == SEG_AUX) byte = aux[o + r];
-            if (kind != SEG_PAD) any = true;
-            w[j >> 2] |= (uint32_t)byte << ((j & 3) * 8);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int32_t c = c0 + u * 256 + tid;
+            if (c < nbody) __stcs(o + c, m ? shift_combine(A[u], B[u], m) : A[u]);
         }
-        if (any) __stcs((uint4*)(dst_tile + (int64_t)c * 16), make_uint4(w[0], w[1], w[2], w[3]));
     }
 }
 
 __global__ void __launch_bounds__(256, 5)
-materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload,
-                   const uint8_t* __restrict__ aux, const int64_t* __restrict__ seg_dst,
-                   const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_base,
-                   const TileDesc* __restrict__ desc, uint8_t* __restrict__ out, int64_t stride,
-                   int64_t tiles_per_slot, int n_hap, int inline_entries) {
+materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload, const uint8_t* __restrict__ aux,
+                   const TileDesc* __restrict__ desc, const RunItem* __restrict__ items, uint8_t* __restrict__ out, int64_t stride,
+                   int64_t tiles_per_slot, int n_hap) {
     // region-major order: consecutive CTAs work on the same tile index of different haplotypes
     const int64_t b = blockIdx.x;
     const int hb = (int)(b % n_hap);
     const int64_t t = b / n_hap;
-    const int64_t x0 = t * TILE_BYTES;
     const int64_t tile = (int64_t)hb * tiles_per_slot + t;
     const int4 dw = __ldg((const int4*)(desc + tile));
-    // record-gather launches: nearly every tile is crossed by record boundaries, so the tile's inline segment entries are
-    // requested together with the descriptor (one memory round trip before the data loads instead of two)
-    int4 ev = make_int4(0, 0, 0, 0);
-    if (inline_entries && threadIdx.x < INLINE_SEGS)
-        ev = __ldg((const int4*)((const SegEntry*)(desc + tiles_per_slot * n_hap) + tile * INLINE_SEGS + threadIdx.x));
-    uint8_t* __restrict__ dst_tile = out + (int64_t)hb * stride + x0;
+    uint8_t* __restrict__ dst_tile = out + (int64_t)hb * stride + t * TILE_BYTES;
     const int tid = threadIdx.x;
     constexpr int CH = TILE_BYTES / 16 / 256;
-    const int nseg = dw.w;
+    const int64_t srcw0 = ((int64_t)(uint32_t)dw.y << 32) | (uint32_t)dw.x;
+    const uint32_t len0 = (uint32_t)dw.z & 0x7fffu, n_more = (uint32_t)dw.z >> 15;
+    const int kind0 = (int)(srcw0 >> SEG_KIND_SHIFT);
 
-    if (nseg == 0) {
-        // ---- uniform path: the whole tile lies inside one forward segment
-        const int64_t srcw = ((int64_t)(uint32_t)dw.y << 32) | (uint32_t)dw.x;
-        const int kind = (int)(srcw >> SEG_KIND_SHIFT);
-        if (kind == SEG_PAD) return;
-        const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
-        const uint8_t* p = base + (srcw & SEG_OFF_MASK);
+    if (len0 == TILE_BYTES && kind0 != SEG_REF_RC) {
+        // ---- the whole tile lies inside one forward segment (n_more is 0 then)
+        const uint8_t* base = kind0 == SEG_REF_FWD ? ref : (kind0 == SEG_PAYLOAD ? payload : aux);
+        const uint8_t* p = base + (srcw0 & SEG_OFF_MASK);
         const unsigned m = (unsigned)((uintptr_t)p & 15u);
         const uint4* q = (const uint4*)(p - m);
         uint4* o = (uint4*)dst_tile;
@@ -288,115 +287,44 @@ materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ 
         }
         return;
     }
-
-    // ---- general path: several segments (or a reverse-complemented one) intersect the tile
-    const int64_t sb = seg_base[hb] + dw.z;
-    if (nseg > MAX_TILE_SEGS) {
-        copy_tile_many_segments(ref, payload, aux, seg_dst + sb, seg_src + sb, nseg, x0, dst_tile);
-        return;
-    }
-    // Segment table of the tile in shared memory, relative to the tile: rel[i] = first output byte of segment i minus x0
-    // (clamped to 32 bits), adj[i] = source offset that corresponds to x0 (forward: src + (x - x0), reverse
-    // complement: src - (x - x0)), kind[i].
-    __shared__ int32_t s_rel[MAX_TILE_SEGS + 1];
-    __shared__ int64_t s_adj[MAX_TILE_SEGS];
-    __shared__ int32_t s_kind[MAX_TILE_SEGS];
-    const int64_t srcw = ((int64_t)(uint32_t)dw.y << 32) | (uint32_t)dw.x;
-    if (inline_entries && (srcw & TILE_INLINE_FLAG)) {
-        if (tid < nseg) { s_rel[tid] = ev.x; s_kind[tid] = ev.y; s_adj[tid] = ((int64_t)(uint32_t)ev.w << 32) | (uint32_t)ev.z; }
-        if (tid == 0) s_rel[nseg] = (int32_t)(uint32_t)dw.x;
-    } else
-    for (int i = tid; i <= nseg; i += 256) {
-        const int64_t r = seg_dst[sb + i] - x0;
-        s_rel[i] = (int32_t)(r < -(1 << 30) ? -(1 << 30) : (r > (1 << 30) ? (1 << 30) : r));
-        if (i < nseg) {
-            const int64_t src = seg_src[sb + i];
-            const int kind = (int)(src >> SEG_KIND_SHIFT);
-            s_kind[i] = kind;
-            s_adj[i] = kind == SEG_REF_RC ? (src & SEG_OFF_MASK) + r : (src & SEG_OFF_MASK) - r;
-        }
-    }
-    __syncthreads();
-    auto find_segment = [&](int xr) -> int {  // last i in [0,nseg) with rel[i] <= xr (rel[0] <= 0 always)
-        int lo = 0;
-        if (nseg <= COUNT_SEARCH_SEGS) {
-            for (int i = 1; i < nseg; i++) lo += s_rel[i] <= xr ? 1 : 0;
-        } else {
-            int hi = nseg;
-            while (hi - lo > 1) {
-                const int mid = (lo + hi) >> 1;
-                if (s_rel[mid] <= xr) lo = mid; else hi = mid;
-            }
-        }
-        return lo;
-    };
-    // Phase 1: every thread resolves its four 16-byte chunks and issues the loads of all the chunks that lie inside one
-    // forward segment (8 aligned 16-byte loads in flight per thread, as in the uniform path). Phase 2: realign + store.
-    // Phase 3: the few chunks that straddle a segment boundary or belong to a reverse-complemented segment: sixteen
-    // independent byte loads each.
-    uint4 A[CH], B[CH];
-    unsigned mis[CH];
-    unsigned vec_mask = 0, slow_mask = 0;
-#pragma unroll
-    for (int u = 0; u < CH; u++) {
-        const int xr = (tid + u * 256) * 16;
-        const int lo = find_segment(xr);
-        const int kind = s_kind[lo];
-        mis[u] = 0;
-        if (xr + 16 > s_rel[lo + 1] || kind == SEG_REF_RC) slow_mask |= 1u << u;
-        else if (kind != SEG_PAD) {
-            const uint8_t* base = kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux);
-            const uint8_t* p = base + (s_adj[lo] + xr);
-            const unsigned m = (unsigned)((uintptr_t)p & 15u);
-            const uint4* q = (const uint4*)(p - m);
-            A[u] = __ldg(q);
-            B[u] = __ldg(q + 1);   // buffers carry >= 32 bytes of slack past their end
-            mis[u] = m; vec_mask |= 1u << u;
-        }
-    }
-#pragma unroll
-    for (int u = 0; u < CH; u++)
-        if ((vec_mask >> u) & 1u) __stcs((uint4*)(dst_tile + (tid + u * 256) * 16), shift_combine(A[u], B[u], mis[u]));
+    // ---- several runs (or a short / reverse-complemented one): the run array is read while the first run is copied
+    const int4* it = (const int4*)(items + dw.w);
+    int4 nxt = make_int4(0, 0, 0, 0);
+    if (n_more) nxt = __ldg(it);
+    copy_run(ref, payload, aux, srcw0, 0, (int32_t)len0, dst_tile);
 #pragma unroll 1
-    for (int u = 0; u < CH; u++) {
-        if (!((slow_mask >> u) & 1u)) continue;
-        const int xr = (tid + u * 256) * 16;
-        int i = find_segment(xr);
-        int rnext = s_rel[i + 1], kind = s_kind[i];
-        int64_t adj = s_adj[i];
-        uint8_t by[16];
-        unsigned rc_mask = 0, any_mask = 0;
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            const int xb = xr + j;
-            while (xb >= rnext) {  // zero-length segments are skipped here as well
-                i++;
-                rnext = s_rel[i + 1]; kind = s_kind[i]; adj = s_adj[i];
-            }
-            const uint8_t* p = kind == SEG_REF_RC ? ref + (adj - xb)
-                                                  : (kind == SEG_REF_FWD ? ref : (kind == SEG_PAYLOAD ? payload : aux)) + (adj + xb);
-            by[j] = 0;
-            if (kind != SEG_PAD) { by[j] = __ldg(p); any_mask |= 1u << j; }
-            if (kind == SEG_REF_RC) rc_mask |= 1u << j;
-        }
-        if (!any_mask) continue;
-        uint32_t w[4] = {0, 0, 0, 0};
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            const uint8_t byte = (rc_mask >> j) & 1u ? complement_base(by[j]) : by[j];
-            w[j >> 2] |= (uint32_t)byte << ((j & 3) * 8);
-        }
-        __stcs((uint4*)(dst_tile + (tid + u * 256) * 16), make_uint4(w[0], w[1], w[2], w[3]));
+    for (uint32_t j = 0; j < n_more; j++) {
+        const int4 cur = nxt;
+        if (j + 1 < n_more) nxt = __ldg(it + j + 1);
+        copy_run(ref, payload, aux, ((int64_t)(uint32_t)cur.y << 32) | (uint32_t)cur.x, cur.z, cur.w, dst_tile);
     }
+}
+
+// Run tables for n_hap slots of tiles_per_slot tiles (count, scan, fill) on stream st.
+static void build_run_tables(sp_ctx* c, cudaStream_t st, const int64_t* seg_dst, const int64_t* seg_src, const int64_t* seg_base, int n_hap,
+                             int64_t tiles_per_slot, int64_t n_segments, DevBuf<TileDesc>& desc, DevBuf<RunItem>& items) {
+    const int64_t ntiles = tiles_per_slot * n_hap;
+    desc.reserve((size_t)ntiles);
+    items.reserve((size_t)(n_segments + ntiles + 64));   // every run but the first of a tile: fewer than segments + tiles
+    c->d_tile_more.reserve((size_t)ntiles + 1); c->d_tile_s0.reserve((size_t)ntiles); c->d_tile_scan.reserve((size_t)ntiles + 1);
+    size_t tmp = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->d_tile_more.p, c->d_tile_scan.p, (int)ntiles, st);
+    c->d_tile_tmp.reserve(tmp + 256);
+    const unsigned grid = (unsigned)((ntiles + 255) / 256);
+    tile_runs_kernel<false><<<grid, 256, 0, st>>>(seg_dst, seg_src, seg_base, n_hap, tiles_per_slot, c->d_tile_s0.p, c->d_tile_more.p, nullptr, nullptr, nullptr);
+    tmp = c->d_tile_tmp.cap;
+    SP_CUDA(cub::DeviceScan::ExclusiveSum(c->d_tile_tmp.p, tmp, c->d_tile_more.p, c->d_tile_scan.p, (int)ntiles, st));
+    tile_runs_kernel<true><<<grid, 256, 0, st>>>(seg_dst, seg_src, seg_base, n_hap, tiles_per_slot, c->d_tile_s0.p, nullptr, c->d_tile_scan.p, desc.p, items.p);
+    c->launches += 3;
+    SP_CUDA(cudaGetLastError());
 }
 
 // ------------------------------------------------------------------------------------------------- host
 static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 
 static void launch_materialise(cudaStream_t st, int64_t ntiles, const uint8_t* ref, const uint8_t* payload, const uint8_t* aux,
-                               const int64_t* seg_dst, const int64_t* seg_src, const int64_t* seg_base, const TileDesc* desc,
-                               uint8_t* out, int64_t stride, int64_t tiles_per_slot, int n_slots, int inline_entries) {
-    materialise_kernel<<<(unsigned)ntiles, 256, 0, st>>>(ref, payload, aux, seg_dst, seg_src, seg_base, desc, out, stride, tiles_per_slot, n_slots, inline_entries);
+                               const TileDesc* desc, const RunItem* items, uint8_t* out, int64_t stride, int64_t tiles_per_slot, int n_slots) {
+    materialise_kernel<<<(unsigned)ntiles, 256, 0, st>>>(ref, payload, aux, desc, items, out, stride, tiles_per_slot, n_slots);
 }
 
 void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, int64_t* out_lengths, int64_t* slot_stride) {
@@ -467,11 +395,7 @@ void plan_haplotypes(sp_ctx* c, int32_t first, int32_t last, int32_t framing, in
     c->tiles_per_slot = c->slot_stride / TILE_BYTES;
     const int64_t ntiles = c->tiles_per_slot * nh;
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "batch too large: reduce the haplotype range");
-    B.tile_desc.reserve(ntiles);
-    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, st>>>(B.seg_dst.p, B.seg_src.p, B.seg_base.p, nh,
-                                                                        c->tiles_per_slot, B.tile_desc.p, 0);
-    c->launches++;
-    SP_CUDA(cudaGetLastError());
+    build_run_tables(c, st, B.seg_dst.p, B.seg_src.p, B.seg_base.p, nh, c->tiles_per_slot, nseg, B.tile_desc, B.items);
     SP_CUDA(cudaEventRecord(c->ev_planned, st));
     c->d_out.reserve((size_t)c->slot_stride * nh, 0.01);
     c->plan_cur = ps;
@@ -486,28 +410,27 @@ void materialise(sp_ctx* c) {
     const int64_t ntiles = c->tiles_per_slot * nh;
     sp_ctx::PlanSet& B = c->plan_set[c->plan_cur];
     SP_CUDA(cudaStreamWaitEvent(c->stream, c->ev_planned, 0));   // no-op when the plan ran on this stream
-    launch_materialise(c->stream, ntiles, c->d_ref.p, c->d_payload.p, B.aux.p, B.seg_dst.p, B.seg_src.p, B.seg_base.p,
-                       B.tile_desc.p, c->d_out.p, c->slot_stride, c->tiles_per_slot, nh, 0);
+    launch_materialise(c->stream, ntiles, c->d_ref.p, c->d_payload.p, B.aux.p, B.tile_desc.p, B.items.p, c->d_out.p, c->slot_stride,
+                       c->tiles_per_slot, nh);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     SP_CUDA(cudaEventRecord(B.ev_used, c->stream));
     c->materialised = true;
 }
 
-// The tiled copy on caller-built segment tables (row D reuses it: records of the length-bin blob -> FASTQ bytes).
+// The tiled copy on caller-built segment tables (rows D, W, F1, F3 reuse it: records -> file bytes).
 // n_slots slots of `stride` bytes; slot s owns segments [seg_base[s], seg_base[s+1]) laid out as plan_kernel does:
-// ascending seg_dst, then a PAD segment at the slot's total length and a sentinel with dst = INT64_MAX.
+// ascending seg_dst, then a PAD segment at the slot's total length and a sentinel with dst = INT64_MAX; n_segments = their
+// total number.
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
-                       int n_slots) {
+                       const int64_t* seg_src, const int64_t* seg_base, int64_t n_segments, uint8_t* out, int64_t stride, int n_slots) {
     const int64_t tiles_per_slot = stride / TILE_BYTES;
     const int64_t ntiles = tiles_per_slot * n_slots;
     if (ntiles <= 0) return;
     if (ntiles >= (int64_t)INT32_MAX) throw Error(SP_ERR_ARG, "tiled copy: too many tiles");
-    // tile_desc holds ntiles descriptors followed by ntiles * INLINE_SEGS inline segment entries (both 16 bytes each)
-    tile_table_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, c->stream>>>(seg_dst, seg_src, seg_base, n_slots, tiles_per_slot, tile_desc, 1);
-    launch_materialise(c->stream, ntiles, src, payload, aux, seg_dst, seg_src, seg_base, tile_desc, out, stride, tiles_per_slot, n_slots, 1);
-    c->launches += 2;
+    build_run_tables(c, c->stream, seg_dst, seg_src, seg_base, n_slots, tiles_per_slot, n_segments, c->d_copy_desc, c->d_copy_items);
+    launch_materialise(c->stream, ntiles, src, payload, aux, c->d_copy_desc.p, c->d_copy_items.p, out, stride, tiles_per_slot, n_slots);
+    c->launches++;
     SP_CUDA(cudaGetLastError());
 }
 

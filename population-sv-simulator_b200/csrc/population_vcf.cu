@@ -20,8 +20,7 @@
 namespace sp {
 
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
-                       int n_slots);
+                       const int64_t* seg_src, const int64_t* seg_base, int64_t n_segments, uint8_t* out, int64_t stride, int n_slots);
 
 namespace {
 
@@ -84,7 +83,6 @@ void upload(sp_ctx* c, DevBuf<int64_t>& d, const std::vector<int64_t>& h) {
 struct VcfDeviceState {
     DevBuf<uint8_t> d_text, d_records, d_files;
     DevBuf<int64_t> d_seg_dst, d_seg_src, d_seg_base;
-    DevBuf<TileDesc> d_desc;
     std::vector<int64_t> rec_off;   // V+1 offsets into d_records (inactive variants have empty records)
     double gather_ms = 0.0;
     int64_t bytes_out = 0;
@@ -96,8 +94,7 @@ static void run_copy(sp_ctx* c, VcfDeviceState& S, SegTables& T, const uint8_t* 
     if (!text.empty()) SP_CUDA(cudaMemcpyAsync(S.d_text.p, text.data(), text.size(), cudaMemcpyHostToDevice, c->stream));
     upload(c, S.d_seg_dst, T.dst); upload(c, S.d_seg_src, T.src); upload(c, S.d_seg_base, T.base);
     out.reserve((size_t)stride * n_slots, 0.05);
-    S.d_desc.reserve((size_t)(stride / TILE_BYTES) * n_slots * (1 + INLINE_SEGS));
-    launch_tiled_copy(c, src, payload, S.d_text.p, S.d_seg_dst.p, S.d_seg_src.p, S.d_seg_base.p, S.d_desc.p, out.p, stride, n_slots);
+    launch_tiled_copy(c, src, payload, S.d_text.p, S.d_seg_dst.p, S.d_seg_src.p, S.d_seg_base.p, (int64_t)T.dst.size(), out.p, stride, n_slots);
     SP_CUDA(cudaStreamSynchronize(c->stream));   // the host vectors above go out of scope with the caller
 }
 
@@ -160,7 +157,7 @@ static void build_record_blob(sp_ctx* c, const PopulationState& P, VcfDeviceStat
 template <class Fill>
 static void emit_files(sp_ctx* c, VcfDeviceState& S, const std::vector<std::string>& paths, Fill fill) {
     const int64_t budget = 2ll << 30;
-    FileSink sink(c->device, 4, 32ll << 20);
+    FileSink& sink = file_sink(c);
     size_t k = 0;
     while (k < paths.size()) {
         Text t;

@@ -28,8 +28,7 @@
 namespace sp {
 
 void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, const uint8_t* aux, const int64_t* seg_dst,
-                       const int64_t* seg_src, const int64_t* seg_base, TileDesc* tile_desc, uint8_t* out, int64_t stride,
-                       int n_slots);
+                       const int64_t* seg_src, const int64_t* seg_base, int64_t n_segments, uint8_t* out, int64_t stride, int n_slots);
 
 struct MixSource {
     DevBuf<uint8_t> records, dropped;
@@ -44,7 +43,6 @@ struct ReadMixState {
     DevBuf<uint64_t> d_key, d_key2;
     DevBuf<int32_t> d_idx, d_idx2;
     DevBuf<int64_t> d_len, d_out_off, d_seg_dst, d_seg_src, d_seg_base;
-    DevBuf<TileDesc> d_tile_first;
     DevBuf<uint8_t> d_aux, d_tmp, d_out;
     int64_t n_reads = 0, out_bytes = 0;
     std::vector<int64_t> h_out_off;
@@ -158,7 +156,6 @@ static void mix_finish(sp_ctx* c, int64_t shuffle_seed) {
     M.out_bytes = A.bytes + (M.n_sources > 1 ? B.bytes : 0);
     for (auto& e : M.ev) if (!e) SP_CUDA(cudaEventCreate(&e));
     const int64_t stride = std::max<int64_t>(TILE_BYTES, (M.out_bytes + TILE_BYTES - 1) / TILE_BYTES * TILE_BYTES);
-    M.d_tile_first.reserve((size_t)(stride / TILE_BYTES) * (1 + INLINE_SEGS));  // descriptors + inline segment entries
     M.d_out.reserve((size_t)stride, 0.02);
     SP_CUDA(cudaEventRecord(M.ev[0], st));
     const size_t n1s = (size_t)std::max<int64_t>(n, 1);
@@ -192,8 +189,7 @@ static void mix_finish(sp_ctx* c, int64_t shuffle_seed) {
     c->launches += 4 + 3;  // four kernels of this file + cub's scans and sort (counted as one each)
     SP_CUDA(cudaGetLastError());
     SP_CUDA(cudaEventRecord(M.ev[1], st));
-    launch_tiled_copy(c, A.records.p, B.records.p, M.d_aux.p, M.d_seg_dst.p, M.d_seg_src.p, M.d_seg_base.p, M.d_tile_first.p,
-                      M.d_out.p, stride, 1);
+    launch_tiled_copy(c, A.records.p, B.records.p, M.d_aux.p, M.d_seg_dst.p, M.d_seg_src.p, M.d_seg_base.p, nseg, M.d_out.p, stride, 1);
     SP_CUDA(cudaEventRecord(M.ev[2], st));
     int64_t total = 0;
     SP_CUDA(cudaMemcpyAsync(&total, M.d_out_off.p + n_kept, 8, cudaMemcpyDeviceToHost, st));
@@ -325,7 +321,7 @@ int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const cha
     if (rc != SP_OK) return rc;
     if (output_file) {   // device -> pinned ring -> file, the writer thread overlapping the copies (csrc/file_sink.h)
         sp::ReadMixState& M = *ctx->mix;
-        sp::FileSink sink(ctx->device, 4, 64ll << 20);
+        sp::FileSink& sink = sp::file_sink(ctx);
         sink.write_file(output_file, M.d_out.p, M.out_bytes, ctx->stream);
         sink.finish();
     }

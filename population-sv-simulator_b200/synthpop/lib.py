@@ -139,6 +139,7 @@ def load() -> C.CDLL:
         "sp_haplotype_read_seed": (C.c_uint32, [C.c_uint32, i32]),
         "sp_test_double_to_string": (C.c_int, [C.c_double, cp, i32]),
         "sp_test_number_format4": (C.c_int, [C.c_double, cp, i32]),
+        "sp_probe_bandwidth": (C.c_int, [vp, i32, i64, i32, i32, i32, P(C.c_double)]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
         "sp_reference_length": (i64, [vp]),
@@ -256,6 +257,12 @@ class Context:
 
     def set_population_stream(self, cuda_stream: int | None):
         self._check(self.lib.sp_set_population_stream(self.h, C.c_void_p(cuda_stream or 0)))
+
+    def probe_bandwidth(self, kind: int, slot_bytes: int, n_slots: int, misalign: int = 9, reps: int = 5) -> float:
+        """Device ms per launch of one of the copy-kernel design probes (csrc/probe.cu)."""
+        ms = C.c_double()
+        self._check(self.lib.sp_probe_bandwidth(self.h, kind, slot_bytes, n_slots, misalign, reps, C.byref(ms)))
+        return ms.value
 
     def synchronize(self):
         self._check(self.lib.sp_synchronize(self.h))
