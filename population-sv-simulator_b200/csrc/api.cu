@@ -315,7 +315,7 @@ void FileSink::drain() {
 void FileSink::finish() { drain(); }
 
 FileSink& file_sink(sp_ctx* c) {
-    if (!c->sink) c->sink = new FileSink(c->device, 4, 32ll << 20);
+    if (!c->sink) c->sink = new FileSink(c->device, 4, 8ll << 20);
     return *c->sink;
 }
 void free_file_sink(sp_ctx* c) {

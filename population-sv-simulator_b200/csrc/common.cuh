@@ -188,7 +188,7 @@ struct sp_ctx {
     double bb_ms[3] = {0.0, 0.0, 0.0};
     int64_t bb_records = 0, bb_bytes = 0;
 
-    // device -> pinned ring -> files, created on first use and kept (pinning 128 MB costs tens of milliseconds)
+    // device -> pinned ring -> files, created on first use and kept (pinning memory costs milliseconds per 10 MB)
     sp::FileSink* sink = nullptr;
 };
 

@@ -37,7 +37,7 @@ private:
     std::string error_;
 };
 
-// The context's sink (4 chunks of 32 MiB), created on first use.
+// The context's sink (4 chunks of 8 MiB), created on first use.
 FileSink& file_sink(sp_ctx* c);
 void free_file_sink(sp_ctx* c);
 

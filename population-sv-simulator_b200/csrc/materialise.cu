@@ -213,7 +213,7 @@ __device__ __forceinline__ uint4 shift_combine(uint4 A, uint4 B, unsigned m) {
 }
 
 // One run: output bytes [a, a+n) of the tile from one source. Every thread of the CTA takes part.
-__device__ __forceinline__ void copy_run(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload, const uint8_t* __restrict__ aux,
+__device__ __noinline__ void copy_run(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ payload, const uint8_t* __restrict__ aux,
                                          int64_t srcw, int32_t a, int32_t n, uint8_t* __restrict__ dst_tile) {
     const int kind = (int)(srcw >> SEG_KIND_SHIFT);
     if (kind == SEG_PAD || n <= 0) return;
@@ -300,16 +300,25 @@ materialise_kernel(const uint8_t* __restrict__ ref, const uint8_t* __restrict__ 
     }
 }
 
-// Run tables for n_hap slots of tiles_per_slot tiles (count, scan, fill) on stream st.
-static void build_run_tables(sp_ctx* c, cudaStream_t st, const int64_t* seg_dst, const int64_t* seg_src, const int64_t* seg_base, int n_hap,
-                             int64_t tiles_per_slot, int64_t n_segments, DevBuf<TileDesc>& desc, DevBuf<RunItem>& items) {
-    const int64_t ntiles = tiles_per_slot * n_hap;
+// Buffers of build_run_tables, so that a caller that times its launches can have the allocations behind it first.
+static void reserve_run_tables(sp_ctx* c, int64_t ntiles, int64_t n_segments, DevBuf<TileDesc>& desc, DevBuf<RunItem>& items) {
     desc.reserve((size_t)ntiles);
     items.reserve((size_t)(n_segments + ntiles + 64));   // every run but the first of a tile: fewer than segments + tiles
     c->d_tile_more.reserve((size_t)ntiles + 1); c->d_tile_s0.reserve((size_t)ntiles); c->d_tile_scan.reserve((size_t)ntiles + 1);
     size_t tmp = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->d_tile_more.p, c->d_tile_scan.p, (int)ntiles, st);
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->d_tile_more.p, c->d_tile_scan.p, (int)ntiles, c->stream);
     c->d_tile_tmp.reserve(tmp + 256);
+}
+void reserve_tiled_copy(sp_ctx* c, int64_t stride, int n_slots, int64_t n_segments) {
+    reserve_run_tables(c, stride / TILE_BYTES * n_slots, n_segments, c->d_copy_desc, c->d_copy_items);
+}
+
+// Run tables for n_hap slots of tiles_per_slot tiles (count, scan, fill) on stream st.
+static void build_run_tables(sp_ctx* c, cudaStream_t st, const int64_t* seg_dst, const int64_t* seg_src, const int64_t* seg_base, int n_hap,
+                             int64_t tiles_per_slot, int64_t n_segments, DevBuf<TileDesc>& desc, DevBuf<RunItem>& items) {
+    const int64_t ntiles = tiles_per_slot * n_hap;
+    reserve_run_tables(c, ntiles, n_segments, desc, items);
+    size_t tmp = 0;
     const unsigned grid = (unsigned)((ntiles + 255) / 256);
     tile_runs_kernel<false><<<grid, 256, 0, st>>>(seg_dst, seg_src, seg_base, n_hap, tiles_per_slot, c->d_tile_s0.p, c->d_tile_more.p, nullptr, nullptr, nullptr);
     tmp = c->d_tile_tmp.cap;
