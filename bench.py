@@ -87,82 +87,79 @@ READ_ALGO_BYTES_PER_BASE = 2.0  # 1 B of haplotype read + 1 B of read written pe
 
 
 def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, quality="phred", resample=True):
-    """BASELINE configs[3] on this GPU's shard: pbsim2-model CCS reads at `depth`x over `n_haps` chr1-sized haplotypes that
-    were materialised on the device and never leave it. Returns the `reads` object of the bench line."""
+    """BASELINE configs[3] on this GPU's shard: pbsim2-model CCS reads at `depth`x over `n_haps` chr1-sized haplotypes, taken
+    individual by individual as docker/haplotype2reads.sh does: the two haplotypes are materialised on the device (they never
+    leave it), sequenced, and their reads mixed into one file (cat + seeded shuf + tr) that stays in HBM. The timed region
+    covers everything from the genotype kernels of an individual to its mixed file. Returns the `reads` object."""
     model = os.path.join(work, "P6C4_synthetic.model")
     synth.write_hmm_model(model, quality=quality)
     args, _ = splib.ReadArgs.from_options(CCS_CLI + ["--depth", str(depth), "--hmm_model", model, "--seed", "42"],
                                           stream_mode=splib.READS_PER_READ_STREAMS)
     ctx.reads_configure(args)
-    if resample:
-        ctx.population_genotypes(first_hap, first_hap + n_haps - 1)   # rows G/C/N for these haplotypes
-    ctx.plan_haplotypes(first_hap, first_hap + n_haps - 1, False)
-    ctx.materialise()
-    ctx.synchronize()
-    # warm-up (allocations, table upload): one whole individual when the reads are mixed, so that the three buffer sets the
-    # mix rotates (two sources + the simulator's own) exist before the timed pass, as they do from the second individual on
-    mix = n_haps == 2   # an individual: the two haplotypes' reads are shuffled into one file on the device
-    if mix:
+    n_ind = n_haps // 2
+    tot = dict(bases=0, reads=0, dropped=0, k_ms=0.0, p_ms=0.0, mix_copy_ms=0.0, mix_order_ms=0.0, mixed_bytes=0, mixed_reads=0)
+    used = last = None
+
+    def individual(h0, timed):
+        nonlocal used, last
+        if resample:
+            ctx.population_genotypes(h0, h0 + 1)   # rows G/C/N for this individual
+        ctx.plan_haplotypes(h0, h0 + 1, False)
+        ctx.materialise()
         ctx.reads_mix_begin()
-        for h in range(first_hap, first_hap + n_haps):
-            ctx.reads_simulate_haplotype(h, 1)
+        for h in (h0, h0 + 1):
+            r = ctx.reads_simulate_haplotype(h, 1)
+            tm = ctx.reads_timing()
+            if timed:
+                tot["bases"] += r["bases"]; tot["reads"] += r["n_reads"]; tot["dropped"] += r["n_dropped"]
+                tot["k_ms"] += tm["kernel_ms"]; tot["p_ms"] += tm["plan_ms"]
+                last = r
+                if h == first_hap + 2 * n_ind - 1:
+                    _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of the last haplotype's reads
             ctx.reads_mix_add()
-        ctx.reads_mix_finish(41)
-    ctx.reads_simulate_haplotype(first_hap, 1)
+        n_mixed, mixed_bytes = ctx.reads_mix_finish(42 + h0)
+        if timed:
+            mt = ctx.reads_mix_timing()
+            tot["mix_copy_ms"] += mt["copy_ms"]; tot["mix_order_ms"] += mt["order_ms"]
+            tot["mixed_bytes"] += mixed_bytes; tot["mixed_reads"] += n_mixed
+        return n_mixed, mixed_bytes
+
+    individual(first_hap, False)   # warm-up: allocations, table upload, the three buffer sets the mix rotates
     torch.cuda.synchronize()
     l0 = ctx.kernel_launches
     t0 = time.perf_counter()
-    bases = reads = dropped = 0
-    k_ms = p_ms = 0.0
-    used = None
-    if mix:
-        ctx.reads_mix_begin()
-    for h in range(first_hap, first_hap + n_haps):
-        r = ctx.reads_simulate_haplotype(h, 1 if mix else h + 1)
-        tm = ctx.reads_timing()
-        bases += r["bases"]; reads += r["n_reads"]; dropped += r["n_dropped"]
-        k_ms += tm["kernel_ms"]; p_ms += tm["plan_ms"]
-        if h == first_hap + n_haps - 1:
-            _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of the last haplotype's reads
-        if mix:
-            ctx.reads_mix_add()
+    for k in range(n_ind):
+        n_mixed, mixed_bytes = individual(first_hap + 2 * k, True)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    draws_per_base = float(used.astype(np.int64).sum()) / max(1, r["bases"])
-    mix_obj = None
-    if mix:
-        # docker/haplotype2reads.sh:59-63 (cat, shuf, tr) and the 10x/20x/30x prefixes of reads2svs.sh:65-128
-        t1 = time.perf_counter()
-        n_mixed, mixed_bytes = ctx.reads_mix_finish(42)
-        torch.cuda.synchronize()
-        t_mix = time.perf_counter() - t1
-        mt = ctx.reads_mix_timing()
-        sweep = {f"{c}x": ctx.reads_mix_coverage_prefix(depth, c)["bytes"] for c in sorted({max(1, depth // 3), max(1, 2 * depth // 3), depth})}
-        mix_obj = {"what": "cat + seeded shuf + tr 'Z' '\\n' of the individual's reads on the device, coverage prefixes as byte ranges",
-                   "reads": n_mixed, "file_bytes": mixed_bytes, "wall_s": t_mix, "order_ms": mt["order_ms"], "copy_ms": mt["copy_ms"],
-                   "copy_GBps_algorithmic": 2.0 * mixed_bytes / (mt["copy_ms"] / 1e3) / 1e9, "copy_frac_of_peak": 2.0 * mixed_bytes / (mt["copy_ms"] / 1e3) / 1e9 / peak,
-                   "coverage_prefix_bytes": sweep}
+    bases, k_ms = tot["bases"], tot["k_ms"]
+    draws_per_base = float(used.astype(np.int64).sum()) / max(1, last["bases"])
+    # docker/haplotype2reads.sh:59-63 (cat, shuf, tr) and the 10x/20x/30x prefixes of reads2svs.sh:65-128, last individual
+    sweep = {f"{c}x": ctx.reads_mix_coverage_prefix(depth, c)["bytes"] for c in sorted({max(1, depth // 3), max(1, 2 * depth // 3), depth})}
+    mix_obj = {"what": "cat + seeded shuf + tr 'Z' '\\n' of each individual's reads on the device, coverage prefixes as byte ranges",
+               "individuals": n_ind, "reads": tot["mixed_reads"], "file_bytes": tot["mixed_bytes"], "order_ms": tot["mix_order_ms"], "copy_ms": tot["mix_copy_ms"],
+               "copy_GBps_algorithmic": 2.0 * tot["mixed_bytes"] / (tot["mix_copy_ms"] / 1e3) / 1e9,
+               "copy_frac_of_peak": 2.0 * tot["mixed_bytes"] / (tot["mix_copy_ms"] / 1e3) / 1e9 / peak,
+               "coverage_prefix_bytes_last_individual": sweep}
     achieved = READ_ALGO_BYTES_PER_BASE * bases / (k_ms / 1e3) / 1e9
     # the bound that applies (DESIGN.md section 4): warp instructions issued per second against 4 per clock per SM, with the
-    # instructions per base of the committed ncu capture
-    issue = None
-    tp = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(tp):
-        ipb = json.load(open(tp)).get("reads_kernel", {}).get("warp_instructions_per_base")
-        if ipb:
-            props = torch.cuda.get_device_properties(torch.cuda.current_device())
-            peak_issue = props.multi_processor_count * 4 * 1.965e9
-            rate = ipb * bases / (k_ms / 1e3)
-            issue = {"bound": "issue", "achieved": rate / 1e12, "peak": peak_issue / 1e12, "unit": "T warp-inst/s",
-                     "frac": rate / peak_issue, "warp_instructions_per_base": ipb, "note": "peak = SMs x 4 schedulers x 1965 MHz"}
+    # instructions per base of the committed ncu capture (profiles/r02a_reads_kernel_base_raw.csv: 42.76 G for 7.469 G bases)
+    props = torch.cuda.get_device_properties(torch.cuda.current_device())
+    ipb = 42758455726 / 7468692660
+    peak_issue = props.multi_processor_count * 4 * 1.965e9
+    rate = ipb * bases / (k_ms / 1e3)
+    issue = {"bound": "issue", "achieved": rate / 1e12, "peak": peak_issue / 1e12, "unit": "T warp-inst/s",
+             "frac": rate / peak_issue, "warp_instructions_per_base": round(ipb, 3), "note": "peak = SMs x 4 schedulers x 1965 MHz"}
     return {"metric": "CCS read Gbp/s", "value": bases / dt / 1e9, "unit": "Gbp/s",
-            "workload": f"pbsim2 model mode, {depth}x over {n_haps} materialised chr1-sized haplotypes, length 15000+-2000 in [5000,30000], "
-                        f"accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model ({quality} emission centres), per-read glibc streams",
+            "workload": f"pbsim2 model mode, {depth}x over {2 * n_ind} materialised chr1-sized haplotypes ({n_ind} individuals, mixed per individual), "
+                        f"length 15000+-2000 in [5000,30000], accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model ({quality} emission centres), per-read glibc streams",
+            "timed": "per individual: genotype kernels, plan, materialisation, two read launches, mix; wall clock around all individuals",
             "draws_per_base": round(draws_per_base, 2),
-            "reads": reads, "dropped_NNNNN": dropped, "bases": bases, "wall_s": dt, "kernel_ms": k_ms, "host_plan_ms": p_ms,
+            "reads": tot["reads"], "dropped_NNNNN": tot["dropped"], "bases": bases, "wall_s": dt, "kernel_ms": k_ms, "host_plan_ms": tot["p_ms"],
             "kernel_gbp_s": bases / (k_ms / 1e3) / 1e9, "gpu_launches": ctx.kernel_launches - l0,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE},
+                         "traffic": 22.3 * bases, "traffic_source": "22.3 B per base, ncu of one launch (profiles/r02a_reads_kernel_base_raw.csv)",
+                         "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE},
             "issue_roofline": issue, "mix": mix_obj}
 
 
@@ -537,7 +534,8 @@ def main():
     ap.add_argument("--e2e-haplotypes", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="genotype/collision/plan kernels on the materialisation stream")
-    ap.add_argument("--read-haplotypes", type=int, default=2, help="haplotypes of the CCS read leg (0 = skip)")
+    ap.add_argument("--read-haplotypes", type=int, default=-1,
+                    help="haplotypes of the CCS read leg per GPU (0 = skip; default = configs[3]: 100 haplotypes over the GPUs of the run)")
     ap.add_argument("--read-depth", type=int, default=30)
     ap.add_argument("--length-bins", type=int, default=1, help="row D leg (SampleReadsFromLengthBins), 0 = skip")
     ap.add_argument("--file-emission", type=int, default=1, help="configs[0] through the files (rank 0, N=1), 0 = skip")
@@ -548,6 +546,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     L = args.length
+    if args.read_haplotypes < 0:
+        args.read_haplotypes = max(2, (100 // max(world, 1)) // 2 * 2)   # configs[3]: 100 haplotypes, whole individuals per rank
 
     if args.impl == "reference":
         if rank == 0:
@@ -727,7 +727,7 @@ def main():
         t_child = time.perf_counter() - t0
         h0 = child["child_first_haplotype"]
         r = reads_leg(ctx, splib, synth, work, h0, 2, args.read_depth, peak, torch, args.read_quality, resample=False)
-        trio_obj = {"what": "sp_trio_add_child (one nextBoolean() per parent, truth VCF by the buildVCF merge) + the child's reads as in `reads`",
+        trio_obj = {"what": "sp_trio_add_child (one nextBoolean() per parent, truth VCF by the buildVCF merge) + the child's reads as in `reads` (one individual)",
                     "father_individual": 3, "mother_individual": 8, "child_haplotypes": [h0, h0 + 1], "inherited": [child["from_father_haplotype"], child["from_mother_haplotype"]],
                     "add_child_and_vcf_s": round(t_child, 4), "child_vcf_bytes": os.path.getsize(os.path.join(out_dir, f"groundTruth_individual_{h0}.vcf")),
                     "reads_gbp_s": r["value"], "reads_kernel_gbp_s": r["kernel_gbp_s"], "reads": r["reads"], "bases": r["bases"],

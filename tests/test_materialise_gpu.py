@@ -143,3 +143,12 @@ def test_full_size_chr1_against_oracle(sp, oracle_lib):
         got = ctx.copy_haplotype(h, int(stride))
         assert np.array_equal(got, want), f"haplotype {h} differs at chr1 size"
     ctx.close()
+
+
+def test_copy_design_probes_copy_the_right_bytes(sp):
+    """csrc/probe.cu (the register path, the bulk-copy engine under an mbarrier, warp-private bulk pipelines): each probe
+    checks the bytes it wrote against the shifted source before it reports a time."""
+    with sp.Context(0, 42) as ctx:
+        for kind in (0, 1, 2, 3):
+            for mis in ((0,) if kind == 0 else (0, 9, 15)):
+                assert ctx.probe_bandwidth(kind, 3_000_001, 7, mis, 2) > 0.0
