@@ -337,6 +337,32 @@ int sp_fastq2length_histogram(sp_ctx* ctx, const char* fastq_file, int32_t bin_l
  * and bytes written. Outputs may be NULL. */
 int sp_build_bins_timing(sp_ctx* ctx, double* index_ms, double* shuffle_ms, double* copy_ms, int64_t* n_records, int64_t* n_bytes);
 
+/* BuildModel.main (src/BuildModel.java:21-47; buildModel/buildModel.sh:16): REPEATMASKER_FILE NROWS TRF_FILE NROWS SEGDUPS_FILE
+ * NROWS REFERENCE_FAI REFERENCE_CYTOBANDS GNOMADSV_FILE ONLY_PASS OUTPUT_DIR VERBOSE. Writes into output_dir the files
+ * SimulateHaplotypes loads (serializeStatistics :1135-1197, serializeRepeatIntervals :446-458, serializeSegdups :563-577):
+ * statistics_svType.txt, statistics_intervalType.txt, statistics_length.txt, statistics_alleleFrequency_{ALL,AFR,AMR,EAS,EUR,OTH}.txt,
+ * statistics_position.txt, repeatIntervals.txt, segdups.txt. The record histograms (collectStatistics :933-1020) and the
+ * allele-frequency sorts (:1079) run on the device; the carried-state scans and every floating-point sum keep the Java's order. */
+typedef struct sp_build_model_args {
+    const char* repeatmasker_file;   /* args[0]: cleaned RepeatMasker table, comma-separated */
+    int32_t repeatmasker_rows;       /* args[1]: capacity the Java allocates; more rows than this is an exception */
+    const char* trf_file;            /* args[2]: cleaned TRF table, comma-separated */
+    int32_t trf_rows;                /* args[3] */
+    const char* segdups_file;        /* args[4]: UCSC segmental duplications, tab-separated with a header line */
+    int32_t segdups_rows;            /* args[5]: must equal the number of data rows */
+    const char* reference_fai;       /* args[6] */
+    const char* reference_cytobands; /* args[7] */
+    const char* gnomad_vcf;          /* args[8] */
+    int32_t only_pass;               /* args[9] == 1 */
+    const char* output_dir;          /* args[10] */
+    int32_t verbose;                 /* args[11] == 1 (the Java passes false to the loaders; only the chr1 summary line is printed) */
+} sp_build_model_args;
+int sp_build_model(sp_ctx* ctx, const sp_build_model_args* args);
+/* Of the last sp_build_model of this process: host seconds of the loaders and the record scan, device milliseconds of the
+ * histogram + sort launches, host seconds of the floating-point passes and the file writes; records counted and allele
+ * frequencies sorted. Outputs may be NULL. */
+int sp_build_model_timing(sp_ctx* ctx, double* parse_seconds, double* device_ms, double* finish_seconds, int64_t* n_records, int64_t* n_allele_frequencies);
+
 #ifdef __cplusplus
 }
 #endif

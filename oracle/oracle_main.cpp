@@ -1,6 +1,6 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY. Command-line front end of the CPU restatement:
 //   synthpop_oracle [--seed S] [--quiet] [--dump-pre-collision FILE] [--draw-log FILE] [--cdf FILE]
-//                   <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|BuildReadLengthBins|Fastq2LengthHistogram> <positional argv of the Java class>
+//                   <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|BuildReadLengthBins|Fastq2LengthHistogram|BuildModel> <positional argv of the Java class>
 // Exit codes follow the Java: 0 ok, 1 uncaught exception, 3 = SampleReadsFromLengthBins coverage unreachable.
 // The seed replaces the reference's unseeded `new Random()` (src/SimulateHaplotypes.java:71) — the one
 // documented deviation from the reference argv (SURVEY.md §8b "Seed").
@@ -11,6 +11,7 @@ int sampleReadsFromLengthBinsMain(const std::vector<std::string>& args, int64_t 
 int annotateVcfMain(const std::vector<std::string>& args);
 int buildReadLengthBinsMain(const std::vector<std::string>& args, int64_t seed);
 int fastq2LengthHistogramMain(const std::vector<std::string>& args);
+int buildModelMain(const std::vector<std::string>& args);
 }
 
 int main(int argc, char** argv) {
@@ -65,6 +66,8 @@ int main(int argc, char** argv) {
             return oracle::buildReadLengthBinsMain(args, seed);
         } else if (cls == "Fastq2LengthHistogram") {
             return oracle::fastq2LengthHistogramMain(args);
+        } else if (cls == "BuildModel") {
+            return oracle::buildModelMain(args);
         }
         fprintf(stderr, "unknown class %s\n", cls.c_str());
         return 2;

@@ -28,7 +28,7 @@ int main(int argc, char** argv) {
         else break;
     }
     if (a >= argc) {
-        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|BuildReadLengthBins|Fastq2LengthHistogram|pbsim|haplotype2reads> <argv of the reference's command>\n");
+        fprintf(stderr, "usage: synthpop [--seed S] [--device D] <SimulateHaplotypes|PrintHaplotypes|SampleReadsFromLengthBins|AnnotateVCF|BuildReadLengthBins|Fastq2LengthHistogram|BuildModel|pbsim|haplotype2reads> <argv of the reference's command>\n");
         return 2;
     }
     const std::string cls = argv[a++];
@@ -135,6 +135,15 @@ int main(int argc, char** argv) {
         // FASTQ_FILE BIN_LENGTH MAX_READ_LENGTH OUTPUT_FILE_HISTOGRAM OUTPUT_FILE_MAX (src/Fastq2LengthHistogram.java:11-16)
         if (args.size() < 5) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
         rc = sp_fastq2length_histogram(ctx, args[0], atoi(args[1]), atoi(args[2]), args[3], args[4]);
+    } else if (cls == "BuildModel") {
+        // REPEATMASKER_FILE NROWS TRF_FILE NROWS SEGDUPS_FILE NROWS REFERENCE_FAI REFERENCE_CYTOBANDS GNOMADSV_FILE ONLY_PASS
+        // OUTPUT_DIR VERBOSE (src/BuildModel.java:22-33)
+        if (args.size() < 12) { fprintf(stderr, "Exception in thread \"main\" java.lang.ArrayIndexOutOfBoundsException\n"); return 1; }
+        sp_build_model_args ma;
+        ma.repeatmasker_file = args[0]; ma.repeatmasker_rows = atoi(args[1]); ma.trf_file = args[2]; ma.trf_rows = atoi(args[3]);
+        ma.segdups_file = args[4]; ma.segdups_rows = atoi(args[5]); ma.reference_fai = args[6]; ma.reference_cytobands = args[7];
+        ma.gnomad_vcf = args[8]; ma.only_pass = atoi(args[9]) == 1; ma.output_dir = args[10]; ma.verbose = atoi(args[11]) == 1;
+        rc = sp_build_model(ctx, &ma);
     } else if (cls == "haplotype2reads") {
         // docker/haplotype2reads.sh:16-24,31-32,53-64 for one individual, without the haplotype_<i>.fa files and the bucket:
         // ID1 LENGTH_MIN LENGTH_MAX LENGTH_MEAN LENGTH_STDEV MAX_COVERAGE REFERENCE_FILE HAPLOTYPE2VARIANTS_FILE VARIANTS_FILE

@@ -107,6 +107,13 @@ class BuildBinsArgs(C.Structure):
                 ("genome_length_haploid", C.c_int64), ("output_prefix", C.c_char_p)]
 
 
+class BuildModelArgs(C.Structure):
+    """sp_build_model_args: positional argv of BuildModel.main (src/BuildModel.java:22-33)."""
+    _fields_ = [("repeatmasker_file", C.c_char_p), ("repeatmasker_rows", C.c_int32), ("trf_file", C.c_char_p), ("trf_rows", C.c_int32),
+                ("segdups_file", C.c_char_p), ("segdups_rows", C.c_int32), ("reference_fai", C.c_char_p), ("reference_cytobands", C.c_char_p),
+                ("gnomad_vcf", C.c_char_p), ("only_pass", C.c_int32), ("output_dir", C.c_char_p), ("verbose", C.c_int32)]
+
+
 def load() -> C.CDLL:
     """dlopen the in-tree libsynthpop_cuda.so and declare every prototype of include/synthpop_cuda.h."""
     global _lib
@@ -189,6 +196,8 @@ def load() -> C.CDLL:
         "sp_build_read_length_bins": (C.c_int, [vp, P(BuildBinsArgs)]),
         "sp_fastq2length_histogram": (C.c_int, [vp, cp, i32, i32, cp, cp]),
         "sp_build_bins_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double), P(C.c_double), P(i64), P(i64)]),
+        "sp_build_model": (C.c_int, [vp, P(BuildModelArgs)]),
+        "sp_build_model_timing": (C.c_int, [vp, P(C.c_double), P(C.c_double), P(C.c_double), P(i64), P(i64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -598,6 +607,22 @@ class Context:
         """Fastq2LengthHistogram.main(args): FASTQ_FILE BIN_LENGTH MAX_READ_LENGTH OUTPUT_FILE_HISTOGRAM OUTPUT_FILE_MAX."""
         a = [str(x) for x in argv]
         self._check(self.lib.sp_fastq2length_histogram(self.h, a[0].encode(), int(a[1]), int(a[2]), a[3].encode(), a[4].encode()))
+
+    def build_model(self, argv):
+        """BuildModel.main(args) (src/BuildModel.java:21-47): REPEATMASKER_FILE NROWS TRF_FILE NROWS SEGDUPS_FILE NROWS REFERENCE_FAI
+        REFERENCE_CYTOBANDS GNOMADSV_FILE ONLY_PASS OUTPUT_DIR VERBOSE."""
+        a = [str(x) for x in argv]
+        if len(a) < 12:
+            raise IndexError("BuildModel takes 12 positional arguments")
+        args = BuildModelArgs(a[0].encode(), int(a[1]), a[2].encode(), int(a[3]), a[4].encode(), int(a[5]), a[6].encode(), a[7].encode(),
+                              a[8].encode(), 1 if int(a[9]) == 1 else 0, a[10].encode(), 1 if int(a[11]) == 1 else 0)
+        self._check(self.lib.sp_build_model(self.h, C.byref(args)))
+
+    def build_model_timing(self):
+        a, b, d = C.c_double(), C.c_double(), C.c_double()
+        n, m = C.c_int64(), C.c_int64()
+        self._check(self.lib.sp_build_model_timing(self.h, C.byref(a), C.byref(b), C.byref(d), C.byref(n), C.byref(m)))
+        return dict(parse_s=a.value, device_ms=b.value, finish_s=d.value, records=n.value, allele_frequencies=m.value)
 
     def build_bins_timing(self):
         a, b, d = C.c_double(), C.c_double(), C.c_double()

@@ -308,3 +308,140 @@ def write_length_bins(prefix: str, n_bins: int, bin_length: int, records_per_bin
         with open(f"{prefix}{b}.bin", "wb") as f:
             f.write(b"".join(parts))
     return total
+
+
+GRCH38_P_ARM_END = {   # approximate last p band end of each chromosome (cytoband file of the reference build)
+    "chr1": 123400000, "chr2": 93900000, "chr3": 90900000, "chr4": 50000000, "chr5": 48800000, "chr6": 59800000,
+    "chr7": 60100000, "chr8": 45200000, "chr9": 43000000, "chr10": 39800000, "chr11": 53400000, "chr12": 35500000,
+    "chr13": 17700000, "chr14": 17200000, "chr15": 19000000, "chr16": 36800000, "chr17": 25100000, "chr18": 18500000,
+    "chr19": 26200000, "chr20": 28100000, "chr21": 12000000, "chr22": 15000000, "chrX": 60600000, "chrY": 10400000,
+}
+
+
+def write_build_model_inputs(root: str, seed: int = GENERATOR_SEED, n_records: int = 40000, n_repeats: int = 120000,
+                             n_trf: int = 30000, n_segdups: int = 3000, drop_type: str | None = None) -> dict:
+    """The nine inputs of BuildModel.main (src/BuildModel.java:22-33) in the formats its loaders parse: a cleaned RepeatMasker
+    table (:101-157: comma-separated, chromosome at column 4, strand at 8, name 9, family 10, consensus range 11-13), a
+    cleaned TRF table (:233-247), a UCSC segdups table with a header (:519-526), reference .fai and cytobands (:666-708)
+    and a gnomAD-SV-style VCF (:933-1020: CHROM without "chr", INFO with SVLEN, SVTYPE, EVIDENCE and the six *_AF keys).
+    Contigs come in the order the Java assumes (chr1, chr10..chr19, chr2, chr20..22, chr3..chr9, chrX, chrY, other).
+    drop_type leaves one SV type out of the autosomes (the case the Java dies on). Returns the argv and the row counts."""
+    os.makedirs(root, exist_ok=True)
+    rng = np.random.default_rng(seed + 23)
+    order = sorted(GRCH38_LENGTHS)   # the lexicographic contig order
+    total = float(sum(GRCH38_LENGTHS.values()))
+    families = [("L1PA3", "LINE/L1"), ("AluSx", "SINE/Alu"), ("ALR/Alpha", "Satellite/centr"), ("(CA)n", "Simple_repeat"),
+                ("AT_rich", "Low_complexity"), ("MLT1B", "LTR/ERVL-MaLR"), ("Charlie1", "DNA/hAT-Charlie"), ("HSATII", "Satellite")]
+    rm_lines, trf_lines, repeat_spots = [], [], {}
+    for chrom in order:
+        L = GRCH38_LENGTHS[chrom]
+        n = max(20, int(n_repeats * L / total))
+        starts = np.sort(rng.integers(1000, L - 20000, size=n))
+        spots = []
+        k = 0
+        while k < n:
+            name, fam = families[int(rng.integers(0, len(families)))]
+            strand = "+" if rng.random() < 0.5 else "C"
+            pos = int(starts[k])
+            cons = int(rng.integers(1, 3000))
+            pieces = 1 + int(rng.random() < 0.3) + int(rng.random() < 0.1)   # fragments the compaction joins
+            for _ in range(pieces):
+                ln = int(rng.integers(30, 3000))
+                a, b = pos + 1, pos + ln
+                ca, cb = cons, cons + ln - 1
+                left = f"({int(rng.integers(0, 500))})"
+                cols = [str(int(rng.integers(200, 30000))), "12.1", "0.5", "1.2", chrom, str(a), str(b), f"({L - b})", strand, name, fam]
+                cols += [str(ca), str(cb), left] if strand == "+" else [left, str(cb), str(ca)]
+                cols.append(str(len(rm_lines) + 1))
+                rm_lines.append(",".join(cols))
+                spots.append(a)
+                if rng.random() < 0.3 and ln > 80:   # another element lying inside or across this one (what buildRepeatIntervals joins)
+                    n2, f2 = families[int(rng.integers(0, len(families)))]
+                    a2 = a + int(rng.integers(1, ln - 40))
+                    b2 = a2 + int(rng.integers(30, 1500))
+                    rm_lines.append(",".join([str(int(rng.integers(200, 30000))), "9.0", "0.0", "0.3", chrom, str(a2), str(b2), f"({L - b2})", "+",
+                                              n2, f2, "1", str(b2 - a2 + 1), "(0)", str(len(rm_lines) + 1)]))
+                    b = max(b, b2)
+                gap = int(rng.integers(0, 60))   # <= 25 joins, above does not
+                pos = b + gap
+                cons = cb + 1 + int(rng.integers(0, 40)) if strand == "+" else max(1, ca - ln - int(rng.integers(0, 40)))
+            k += 1
+            while k < n and int(starts[k]) <= pos:   # keep the table sorted by start
+                k += 1
+        repeat_spots[chrom] = np.array(spots, dtype=np.int64)
+        m = max(5, int(n_trf * L / total))
+        tstarts = np.sort(rng.integers(1000, L - 5000, size=m))
+        for j in range(m):
+            a = int(tstarts[j]) if rng.random() < 0.7 else int(repeat_spots[chrom][int(rng.integers(0, len(spots)))]) + int(rng.integers(-40, 40))
+            a = max(1, a)
+            trf_lines.append((chrom, a, a + int(rng.integers(25, 600))))
+    # TRF rows sorted by start inside a contig, as the UCSC table is
+    trf_lines.sort(key=lambda t: (order.index(t[0]), t[1]))
+    for extra in ("chr1_KI270706v1_random", "chrM"):
+        rm_lines.append(",".join(["300", "1.0", "0.0", "0.0", extra, "10", "200", "(0)", "+", "L1PA3", "LINE/L1", "1", "191", "(0)", "1"]))
+    seg_rows = []
+    for _ in range(n_segdups):
+        chrom = order[int(rng.integers(0, len(order)))]
+        a = int(rng.integers(10000, GRCH38_LENGTHS[chrom] - 400000))
+        seg_rows.append((chrom, a, a + int(rng.integers(1000, 300000))))
+    seg_rows.append(("chrUn_KI270742v1", 100, 5000))
+    files = {k: os.path.join(root, v) for k, v in dict(rm="repeatmasker.csv", trf="trf.csv", seg="segdups.tsv", fai="reference.fa.fai",
+                                                        cyto="cytobands.txt", vcf="gnomad_sv.vcf").items()}
+    with open(files["rm"], "w") as f:
+        f.write("\n".join(rm_lines) + "\n")
+    with open(files["trf"], "w") as f:
+        f.write("".join(f"{c},{a},{b},trf,{int(rng.integers(1, 60))},{b - a}\n" for c, a, b in trf_lines))
+    with open(files["seg"], "w") as f:
+        f.write("#bin\tchrom\tchromStart\tchromEnd\tname\n")
+        f.write("".join(f"{585 + i % 7}\t{c}\t{a}\t{b}\t{c}:{a}\n" for i, (c, a, b) in enumerate(seg_rows)))
+    with open(files["fai"], "w") as f:
+        for chrom in list(GRCH38_LENGTHS) + ["chrM", "chr1_KI270706v1_random"]:
+            f.write(f"{chrom}\t{GRCH38_LENGTHS.get(chrom, 16569)}\t6\t60\t61\n")
+    with open(files["cyto"], "w") as f:
+        for chrom in GRCH38_LENGTHS:
+            p, L = GRCH38_P_ARM_END[chrom], GRCH38_LENGTHS[chrom]
+            f.write(f"{chrom}\t0\t{p // 2}\tp21.1\tgneg\n{chrom}\t{p // 2}\t{p}\tp11.1\tacen\n{chrom}\t{p}\t{(p + L) // 2}\tq11\tacen\n{chrom}\t{(p + L) // 2}\t{L}\tq21\tgpos50\n")
+        f.write("chrM\t0\t16569\t\t\n")
+    type_pool = ["DEL"] * 45 + ["DUP"] * 20 + ["INS"] * 25 + ["INV"] * 3 + ["MCNV"] * 2 + ["BND"] * 3 + ["CPX"] * 2
+    evidence_pool = ["SR", "PE", "RD", "PE,SR", "BAF,RD", "PE,RD,SR", "RD,SR"]
+    filter_pool = ["PASS"] * 8 + ["MULTIALLELIC", "UNRESOLVED", "PCRPLUS_ENRICHED", "PESR_GT_OVERDISPERSION;UNSTABLE_AF_PCRMINUS"]
+    n_vcf = 0
+    with open(files["vcf"], "w") as f:
+        f.write("##fileformat=VCFv4.2\n##source=synthetic gnomAD-SV style records\n#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\n")
+        for chrom in order:
+            L = GRCH38_LENGTHS[chrom]
+            n = max(50, int(n_records * L / total))
+            near = repeat_spots[chrom][rng.integers(0, len(repeat_spots[chrom]), size=n)] + rng.integers(-1500, 1500, size=n)
+            free = rng.integers(1, L - 1, size=n)
+            pos = np.sort(np.clip(np.where(rng.random(n) < 0.6, near, free), 1, L - 1))
+            autosome = chrom not in ("chrX", "chrY")
+            for j in range(n):
+                t = type_pool[int(rng.integers(0, len(type_pool)))]
+                if t == drop_type and autosome:
+                    t = "DEL"
+                u = rng.random()
+                ln = int(rng.integers(50, 400)) if u < 0.5 else (int(rng.integers(400, 20000)) if u < 0.9 else int(rng.integers(20000, 3000000)))
+                if t == "DEL" and 5000 <= ln < 60000:
+                    ln = (ln // 1000) * 1000   # the read-depth caller's 1 kb steps the smoothing is there for
+                if rng.random() < 0.03:
+                    ln = int(rng.integers(-1, 50))
+                svlen = -ln if (t == "DEL" and rng.random() < 0.2) else ln
+                afs = np.minimum(1.0, rng.beta(0.25, 6.0, size=6) + 1.0 / 21694.0)
+                if not autosome and rng.random() < 0.2:
+                    afs[0] = 1.3   # hemizygous calls: the reason the Java leaves X and Y out
+                fmt = [repr(float(x)) if rng.random() < 0.5 else f"{x:.6g}" for x in afs]
+                info = (f"END={int(pos[j]) + abs(ln)};SVTYPE={t};" + (f"SVLEN={svlen};" if rng.random() > 0.01 else "") +
+                        f"CHR2={chrom[3:]};ALGORITHMS=manta;EVIDENCE={evidence_pool[int(rng.integers(0, len(evidence_pool)))]};PROTEIN_CODING__INTERGENIC;"
+                        f"AN=21694;AC={int(afs[0] * 21694)};AF={fmt[0]};N_BI_GENOS=10847;AFR_AN=9534;AFR_AF={fmt[1]};AMR_AN=1952;AMR_AF={fmt[2]};"
+                        f"EAS_AN=2416;EAS_AF={fmt[3]};EUR_AN=7624;EUR_AF={fmt[4]};OTH_AN=168;OTH_AF={fmt[5]};POPMAX_AF={max(afs):.6g}")
+                f.write(f"{chrom[3:]}\t{int(pos[j])}\tgnomAD-SV_v2.1_{t}_{chrom[3:]}_{j}\tN\t<{t}>\t{int(rng.integers(1, 999))}\t{filter_pool[int(rng.integers(0, len(filter_pool)))]}\t{info}\n")
+                n_vcf += 1
+        f.write("GL000192.1\t100\tx\tN\t<DEL>\t1\tPASS\tEND=300;SVTYPE=DEL;SVLEN=200;EVIDENCE=SR;AF=0.1;\n")
+    out_dir = os.path.join(root, "model_out")
+    os.makedirs(out_dir, exist_ok=True)
+    argv = [files["rm"], len(rm_lines), files["trf"], len(trf_lines), files["seg"], len(seg_rows), files["fai"], files["cyto"], files["vcf"], 1, out_dir, 0]
+    return dict(argv=argv, files=files, out_dir=out_dir, n_vcf_records=n_vcf, n_repeatmasker=len(rm_lines), n_trf=len(trf_lines), n_segdups=len(seg_rows))
+
+
+BUILD_MODEL_OUTPUTS = ("statistics_svType.txt", "statistics_intervalType.txt", "statistics_length.txt", "statistics_position.txt",
+                       "repeatIntervals.txt", "segdups.txt") + tuple(f"statistics_alleleFrequency_{p}.txt" for p in AF_NAMES)
