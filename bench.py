@@ -520,6 +520,25 @@ def next_rows_leg(splib, synth, work, local_rank, emission_dir, cpu_baseline=Tru
         t0 = time.perf_counter()
         subprocess.run([oracle, "--seed", "42", "BuildReadLengthBins"] + argv_o, check=True, stderr=subprocess.DEVNULL)
         out["build_read_length_bins"]["cpu_port_wall_s"] = round(time.perf_counter() - t0, 3)
+    # BuildModel (rank 4): synthetic gnomAD-SV-shaped records and annotation tracks over the GRCh38 karyotype
+    bm = synth.write_build_model_inputs(os.path.join(work, "bm_in"), n_records=120_000, n_repeats=300_000, n_trf=60_000, n_segdups=5_000)
+    argv = [str(x) for x in bm["argv"]]
+    with splib.Context(local_rank, 42) as ctx:
+        t0 = time.perf_counter()
+        ctx.build_model(argv)
+        t = time.perf_counter() - t0
+        tm = ctx.build_model_timing()
+    out["build_model"] = {"workload": f"BuildModel, {bm['n_vcf_records']} VCF records, {bm['n_repeatmasker']} RepeatMasker + {bm['n_trf']} TRF + {bm['n_segdups']} segdup rows",
+                          "wall_s": round(t, 3), "load_and_scan_s": round(tm["parse_s"], 3), "device_ms": round(tm["device_ms"], 3),
+                          "float_passes_and_files_s": round(tm["finish_s"], 3), "records_counted": tm["records"], "allele_frequencies_sorted": tm["allele_frequencies"]}
+    if cpu_baseline:
+        odir = os.path.join(work, "bm_oracle")
+        os.makedirs(odir, exist_ok=True)
+        t0 = time.perf_counter()
+        subprocess.run([oracle, "BuildModel"] + argv[:10] + [odir, "0"], check=True, stderr=subprocess.DEVNULL)
+        out["build_model"]["cpu_port_wall_s"] = round(time.perf_counter() - t0, 3)
+        out["build_model"]["files_identical_to_cpu_port"] = all(
+            open(os.path.join(odir, f), "rb").read() == open(os.path.join(bm["out_dir"], f), "rb").read() for f in synth.BUILD_MODEL_OUTPUTS)
     return out
 
 

@@ -327,7 +327,15 @@ void spread(std::vector<double>& out, int from, int to, double per_bp) {
     out[b1] += per_bp * (to + 1 - b1 * Q);
 }
 
-void put(std::string& s, double d) { s += java_double_to_string(d); s += ','; }
+// cumulative rows are long runs of one value: format a value once per run
+void put(std::string& s, double d) {
+    static thread_local uint64_t last_bits = 0;
+    static thread_local std::string last_text;
+    uint64_t bits;
+    memcpy(&bits, &d, 8);
+    if (last_text.empty() || bits != last_bits) { last_text = java_double_to_string(d); last_bits = bits; }
+    s += last_text; s += ',';
+}
 void write_file(const std::string& path, const std::string& text) {
     FILE* f = fopen(path.c_str(), "wb");
     if (!f) java("FileNotFoundException: " + path);

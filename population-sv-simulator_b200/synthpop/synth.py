@@ -319,15 +319,20 @@ GRCH38_P_ARM_END = {   # approximate last p band end of each chromosome (cytoban
 
 
 def write_build_model_inputs(root: str, seed: int = GENERATOR_SEED, n_records: int = 40000, n_repeats: int = 120000,
-                             n_trf: int = 30000, n_segdups: int = 3000, drop_type: str | None = None) -> dict:
+                             n_trf: int = 30000, n_segdups: int = 3000, drop_type: str | None = None, scale: int = 1,
+                             max_sv_length: int = 3000000) -> dict:
     """The nine inputs of BuildModel.main (src/BuildModel.java:22-33) in the formats its loaders parse: a cleaned RepeatMasker
     table (:101-157: comma-separated, chromosome at column 4, strand at 8, name 9, family 10, consensus range 11-13), a
     cleaned TRF table (:233-247), a UCSC segdups table with a header (:519-526), reference .fai and cytobands (:666-708)
     and a gnomAD-SV-style VCF (:933-1020: CHROM without "chr", INFO with SVLEN, SVTYPE, EVIDENCE and the six *_AF keys).
     Contigs come in the order the Java assumes (chr1, chr10..chr19, chr2, chr20..22, chr3..chr9, chrX, chrY, other).
-    drop_type leaves one SV type out of the autosomes (the case the Java dies on). Returns the argv and the row counts."""
+    drop_type leaves one SV type out of the autosomes (the case the Java dies on). scale divides every chromosome length
+    (a karyotype small enough to run SimulateHaplotypes on the result); max_sv_length caps SVLEN. Returns the argv and the
+    row counts."""
     os.makedirs(root, exist_ok=True)
     rng = np.random.default_rng(seed + 23)
+    GRCH38_LENGTHS = {c: v // scale for c, v in globals()["GRCH38_LENGTHS"].items()}
+    GRCH38_P_ARM_END = {c: v // scale for c, v in globals()["GRCH38_P_ARM_END"].items()}
     order = sorted(GRCH38_LENGTHS)   # the lexicographic contig order
     total = float(sum(GRCH38_LENGTHS.values()))
     families = [("L1PA3", "LINE/L1"), ("AluSx", "SINE/Alu"), ("ALR/Alpha", "Satellite/centr"), ("(CA)n", "Simple_repeat"),
@@ -421,6 +426,7 @@ def write_build_model_inputs(root: str, seed: int = GENERATOR_SEED, n_records: i
                     t = "DEL"
                 u = rng.random()
                 ln = int(rng.integers(50, 400)) if u < 0.5 else (int(rng.integers(400, 20000)) if u < 0.9 else int(rng.integers(20000, 3000000)))
+                ln = min(ln, max_sv_length)
                 if t == "DEL" and 5000 <= ln < 60000:
                     ln = (ln // 1000) * 1000   # the read-depth caller's 1 kb steps the smoothing is there for
                 if rng.random() < 0.03:
@@ -440,7 +446,7 @@ def write_build_model_inputs(root: str, seed: int = GENERATOR_SEED, n_records: i
     out_dir = os.path.join(root, "model_out")
     os.makedirs(out_dir, exist_ok=True)
     argv = [files["rm"], len(rm_lines), files["trf"], len(trf_lines), files["seg"], len(seg_rows), files["fai"], files["cyto"], files["vcf"], 1, out_dir, 0]
-    return dict(argv=argv, files=files, out_dir=out_dir, n_vcf_records=n_vcf, n_repeatmasker=len(rm_lines), n_trf=len(trf_lines), n_segdups=len(seg_rows))
+    return dict(argv=argv, files=files, out_dir=out_dir, n_vcf_records=n_vcf, chr1_length=GRCH38_LENGTHS["chr1"], n_repeatmasker=len(rm_lines), n_trf=len(trf_lines), n_segdups=len(seg_rows))
 
 
 BUILD_MODEL_OUTPUTS = ("statistics_svType.txt", "statistics_intervalType.txt", "statistics_length.txt", "statistics_position.txt",

@@ -253,7 +253,8 @@ def test_gpu_build_model_hand_case_and_errors(sp, oracle_bin, tmp_path):
         bad[5] = "4"
         with pytest.raises(sp.SynthpopError, match="NullPointerException"):
             ctx.build_model(bad)
-        open(argv[8], "w").write(open(argv[8]).read().replace(";POPMAX_AF=0.5", ""))
+        vcf = open(argv[8]).read().replace(";POPMAX_AF=0.5", "")
+        open(argv[8], "w").write(vcf)
         with pytest.raises(sp.SynthpopError, match="StringIndexOutOfBoundsException"):
             ctx.build_model(argv)
 
@@ -290,3 +291,28 @@ def test_gpu_build_model_dies_like_the_java_when_a_type_has_no_autosomal_record(
     with sp.Context(0, 1) as ctx:
         with pytest.raises(sp.SynthpopError, match="ArrayIndexOutOfBoundsException"):
             ctx.build_model(argv)
+
+
+@pytest.mark.gpu
+def test_gpu_built_model_feeds_simulate_haplotypes(sp, oracle_bin, tmp_path):
+    """BuildModel -> SimulateHaplotypes through the files: the model directory, repeatIntervals.txt and segdups.txt written
+    by the CUDA path are loaded by sp_simulate_population and by the oracle's SimulateHaplotypes; both must agree."""
+    from synthpop import synth
+    from test_population_gpu import _cmp_dirs
+    r = synth.write_build_model_inputs(str(tmp_path / "bm"), seed=5, scale=25, max_sv_length=10000)
+    with sp.Context(0, 11) as ctx:
+        ctx.build_model(r["argv"])
+    model, L = r["out_dir"], r["chr1_length"]
+    bases, _, _ = synth.random_reference(L, 5)
+    ref, ins = str(tmp_path / "chr1.fa"), str(tmp_path / "insertions.txt")
+    synth.write_fasta(ref, "chr1", bases)
+    synth.write_insertions(ins, 2500, 5, max_len=10500)   # the smoothing leaks INS mass four bins past 10000
+    n_ind = 4
+    want, got = str(tmp_path / "want"), str(tmp_path / "got")
+    os.makedirs(want), os.makedirs(got)
+    argv = [model, "EUR", ref, model + "/repeatIntervals.txt", model + "/segdups.txt", ins, "2500", "0.01", "400", str(n_ind)]
+    subprocess.run([oracle_bin, "--quiet", "--seed", "77", "SimulateHaplotypes"] + argv + [want], check=True)
+    with sp.Context(0, 77) as ctx:
+        ctx.simulate_haplotypes(argv + [got])
+    _cmp_dirs(want, got, n_ind)
+    assert os.path.getsize(os.path.join(got, "groundTruth_joint.vcf")) > 20000
