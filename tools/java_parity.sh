@@ -57,6 +57,48 @@ for d in java oracle ${WITH_CLI:+cli}; do
     cli)    "$CLI" AnnotateVCF "$W/$d/list.txt" 10 100 "${ARGV[2]}" "${ARGV[3]}" "${ARGV[4]}";;
   esac
 done
+# BuildModel on the synthetic tracks and gnomAD-SV-shaped records
+python - "$ROOT" "$W" <<'PY'
+import sys, os
+root, w = sys.argv[1], sys.argv[2]
+sys.path.insert(0, os.path.join(root, "population-sv-simulator_b200"))
+from synthpop import synth
+r = synth.write_build_model_inputs(os.path.join(w, "bm_in"))
+open(os.path.join(w, "bm_argv.txt"), "w").write("\n".join(str(x) for x in r["argv"]))
+PY
+mapfile -t BM < "$W/bm_argv.txt"
+for d in java oracle ${WITH_CLI:+cli}; do
+  mkdir -p "$W/$d/model"
+  BM[10]="$W/$d/model"
+  case $d in
+    java)   "${JAVA[@]}" BuildModel "${BM[@]}";;
+    oracle) "$ORACLE" BuildModel "${BM[@]}";;
+    cli)    "$CLI" BuildModel "${BM[@]}";;
+  esac
+done
+# BuildReadLengthBins on a synthetic FASTQ, then SampleReadsFromLengthBins from each implementation's own bins
+python - "$W" <<'PY'
+import sys, os
+import numpy as np
+w = sys.argv[1]
+rng = np.random.default_rng(3)
+acgt = np.frombuffer(b"ACGT", np.uint8)
+with open(os.path.join(w, "reads.fastq"), "wb") as f:
+    for k in range(20000):
+        ln = max(60, int(rng.normal(1750, 350) if rng.random() < 0.45 else rng.normal(3750, 350)))
+        f.write(b"@r%d\n" % k + acgt[rng.integers(0, 4, ln)].tobytes() + b"\n+\n" + rng.integers(53, 93, ln).astype(np.uint8).tobytes() + b"\n")
+open(os.path.join(w, "fastq_list.txt"), "w").write(os.path.join(w, "reads.fastq") + "\n")
+PY
+for d in java oracle ${WITH_CLI:+cli}; do
+  mkdir -p "$W/$d/bins"
+  B=("$W/fastq_list.txt" 500 6000 3100000 "$W/$d/bins/b_")
+  S=(1750 350 3750 350 0.45 500 6000 "$W/$d/bins/b_" 200000 3.0 "$W/$d/bins/sampled.fastq")
+  case $d in
+    java)   "${JAVA[@]}" BuildReadLengthBins "${B[@]}"; "${JAVA[@]}" SampleReadsFromLengthBins "${S[@]}";;
+    oracle) "$ORACLE" --seed $SEED BuildReadLengthBins "${B[@]}"; "$ORACLE" --seed $SEED SampleReadsFromLengthBins "${S[@]}";;
+    cli)    "$CLI" --seed $SEED BuildReadLengthBins "${B[@]}"; "$CLI" --seed $SEED SampleReadsFromLengthBins "${S[@]}";;
+  esac
+done
 fail=0
 for d in oracle ${WITH_CLI:+cli}; do
   while IFS= read -r f; do
