@@ -56,6 +56,46 @@ probe_register_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out
     for (int u = 0; u < 4; u++) __stcs(o + u * 256 + tid, m ? pb_shift(A[u], B[u], m) : A[u]);
 }
 
+// kind 7: store only, but every 16 bytes differ (a hash of the address) instead of three constants and the thread index
+__global__ void __launch_bounds__(256, 5)
+probe_store_hashed_kernel(uint8_t* __restrict__ out, int64_t stride, int64_t tiles_per_slot, int n_slots) {
+    const int64_t b = blockIdx.x;
+    const int hb = (int)(b % n_slots);
+    const int64_t t = b / n_slots;
+    uint4* o = (uint4*)(out + (int64_t)hb * stride + t * PB_TILE);
+    uint32_t x = (uint32_t)b * 2654435761u ^ (threadIdx.x * 40503u + 0x9E3779B9u);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        uint4 v;
+        x ^= x << 13; x ^= x >> 17; x ^= x << 5; v.x = x;
+        x ^= x << 13; x ^= x >> 17; x ^= x << 5; v.y = x;
+        x ^= x << 13; x ^= x >> 17; x ^= x << 5; v.z = x;
+        x ^= x << 13; x ^= x >> 17; x ^= x << 5; v.w = x;
+        __stcs(o + u * 256 + threadIdx.x, v);
+    }
+}
+
+// kinds 4-6: source-stationary. A CTA loads its 16 KiB source tile once and stores it into `group` slots (all of them, 25
+// or 5): what the stream would cost if the 124 repeat reads of a reference tile never went to L2 at all.
+__global__ void __launch_bounds__(256, 5)
+probe_stationary_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ out, int64_t stride, int64_t tiles_per_slot, int n_slots, int group) {
+    const int n_groups = (n_slots + group - 1) / group;
+    const int64_t b = blockIdx.x;
+    const int g = (int)(b % n_groups);
+    const int64_t t = b / n_groups;
+    const uint4* q = (const uint4*)(src + t * PB_TILE);
+    const int tid = threadIdx.x;
+    uint4 A[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) A[u] = __ldg(q + u * 256 + tid);
+    const int h1 = min(n_slots, (g + 1) * group);
+    for (int hb = g * group; hb < h1; hb++) {
+        uint4* o = (uint4*)(out + (int64_t)hb * stride + t * PB_TILE);
+#pragma unroll
+        for (int u = 0; u < 4; u++) __stcs(o + u * 256 + tid, A[u]);
+    }
+}
+
 __global__ void probe_fill_kernel(uint8_t* p, int64_t n) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = (uint8_t)(i % 251);
 }
@@ -180,7 +220,8 @@ probe_bulk_warp_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ ou
 }
 
 void probe_bandwidth(sp_ctx* c, int kind, int64_t slot_bytes, int n_slots, int misalign, int reps, double* ms_out) {
-    if (slot_bytes <= 0 || n_slots <= 0 || reps <= 0 || misalign < 0 || misalign > 4096) throw Error(SP_ERR_ARG, "probe: bad arguments");
+    if (slot_bytes <= 0 || n_slots <= 0 || reps <= 0 || misalign < 0 || misalign > 4096 || kind < 0 || kind > 7 || (kind >= 4 && misalign != 0))
+        throw Error(SP_ERR_ARG, "probe: bad arguments");
     const int64_t tiles_per_slot = (slot_bytes + PB_TILE - 1) / PB_TILE, stride = tiles_per_slot * PB_TILE;
     const int64_t n_tiles = tiles_per_slot * n_slots;
     if (n_tiles >= INT32_MAX) throw Error(SP_ERR_ARG, "probe: too many tiles");
@@ -202,7 +243,13 @@ void probe_bandwidth(sp_ctx* c, int kind, int64_t slot_bytes, int n_slots, int m
         if (kind == 0) probe_store_kernel<<<(unsigned)n_tiles, 256, 0, st>>>(out.p, stride, tiles_per_slot, n_slots);
         else if (kind == 1) probe_register_kernel<<<(unsigned)n_tiles, 256, 0, st>>>(src.p, out.p, stride, tiles_per_slot, n_slots, misalign);
         else if (kind == 2) probe_bulk_kernel<<<c->sm_count * 4, 256, smem, st>>>(src.p, out.p, stride, tiles_per_slot, n_slots, misalign, err.p);
-        else probe_bulk_warp_kernel<<<c->sm_count * 4, 256, smem_w, st>>>(src.p, out.p, stride, tiles_per_slot, n_slots, misalign, err.p);
+        else if (kind == 3) probe_bulk_warp_kernel<<<c->sm_count * 4, 256, smem_w, st>>>(src.p, out.p, stride, tiles_per_slot, n_slots, misalign, err.p);
+        else if (kind == 7) probe_store_hashed_kernel<<<(unsigned)n_tiles, 256, 0, st>>>(out.p, stride, tiles_per_slot, n_slots);
+        else {
+            const int group = kind == 4 ? n_slots : (kind == 5 ? 25 : 5);
+            const int64_t n_cta = tiles_per_slot * ((n_slots + group - 1) / group);
+            probe_stationary_kernel<<<(unsigned)n_cta, 256, 0, st>>>(src.p, out.p, stride, tiles_per_slot, n_slots, group);
+        }
         c->launches++;
     };
     launch();   // warm-up
@@ -217,7 +264,7 @@ void probe_bandwidth(sp_ctx* c, int kind, int64_t slot_bytes, int n_slots, int m
     SP_CUDA(cudaMemcpy(&h_err, err.p, 4, cudaMemcpyDeviceToHost));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (h_err) throw Error(SP_ERR, "probe: the bulk-copy barrier did not complete");
-    if (kind >= 1) {   // the copy must be right before its time means anything: out[slot][x] = src[x + misalign]
+    if (kind >= 1 && kind != 7) {   // the copy must be right before its time means anything: out[slot][x] = src[x + misalign]
         uint8_t probe[4096];
         const int64_t at[3] = {0, (tiles_per_slot / 2) * PB_TILE + 5000, stride - 4096};
         for (int slot : {0, n_slots - 1})

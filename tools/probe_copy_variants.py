@@ -13,8 +13,12 @@ L = int(os.environ.get("PROBE_L", 248_956_422))
 N = int(os.environ.get("PROBE_SLOTS", 125))
 out = {"slot_bytes": L, "n_slots": N}
 with sp.Context(0, 42) as ctx:
-    for kind, name in ((0, "store_only"), (1, "register_copy"), (2, "bulk_copy_mbarrier"), (3, "bulk_copy_warp_pipelines")):
-        for mis in ((0,) if kind == 0 else (0, 9)):
+    for kind, name in ((0, "store_only"), (1, "register_copy"), (2, "bulk_copy_mbarrier"), (3, "bulk_copy_warp_pipelines"),
+                       (4, "source_stationary_all_slots"), (5, "source_stationary_25_slots"), (6, "source_stationary_5_slots"),
+                       (7, "store_only_hashed_data")):
+        if os.environ.get("PROBE_KINDS") and str(kind) not in os.environ["PROBE_KINDS"].split(","):
+            continue
+        for mis in ((0,) if kind in (0, 4, 5, 6, 7) else (0, 9)):
             ms = ctx.probe_bandwidth(kind, L, N, mis, int(os.environ.get("PROBE_REPS", 5)))
             out[f"{name}_misalign{mis}"] = {"ms": round(ms, 4), "written_GBps": round(L * N / ms / 1e6, 1)}
             print(name, mis, out[f"{name}_misalign{mis}"], file=sys.stderr, flush=True)
