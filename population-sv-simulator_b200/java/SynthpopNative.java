@@ -4,7 +4,7 @@ import static java.lang.foreign.ValueLayout.*;
 
 /**
  * Panama FFM (JDK 22+) binding of libsynthpop_cuda.so: one downcall handle per entry point of include/synthpop_cuda.h
- * that the three command-line classes need. Not compiled in the build image (no JDK there); compile where a JDK
+ * that the command-line classes of this directory need. Not compiled in the build image (no JDK there); compile where a JDK
  * exists with `javac -cp commons-math3-3.6.1.jar *.java` and run with `--enable-native-access=ALL-UNNAMED
  * -Djava.library.path=<dir of libsynthpop_cuda.so>`.
  */
@@ -49,6 +49,32 @@ final class SynthpopNative {
             ADDRESS.withName("cumulative"), JAVA_INT.withName("bin_length"), JAVA_INT.withName("max_read_length"),
             ADDRESS.withName("bins_prefix"), JAVA_LONG.withName("genome_length_each_haplotype"),
             JAVA_DOUBLE.withName("target_coverage_each_haplotype"), ADDRESS.withName("output_fastq_file"));
+
+    // the rows either side of the path (SURVEY.md section 8f ranks 2-4)
+    static final MethodHandle sp_annotate_vcf = h("sp_annotate_vcf", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle sp_build_read_length_bins = h("sp_build_read_length_bins", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle sp_fastq2length_histogram = h("sp_fastq2length_histogram",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS));
+    static final MethodHandle sp_build_model = h("sp_build_model", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+
+    /** sp_annotate_args: argv of AnnotateVCF.main, src/AnnotateVCF.java:96-110. */
+    static final StructLayout ANNOTATE_ARGS = MemoryLayout.structLayout(
+            ADDRESS.withName("input_files_list"), JAVA_INT.withName("min_distance"), JAVA_INT.withName("max_distance"),
+            ADDRESS.withName("reference_file"), ADDRESS.withName("repeat_intervals_file"), ADDRESS.withName("segdups_file"));
+
+    /** sp_build_bins_args: argv of BuildReadLengthBins.main, src/BuildReadLengthBins.java:21-27. */
+    static final StructLayout BUILD_BINS_ARGS = MemoryLayout.structLayout(
+            ADDRESS.withName("input_files_list"), JAVA_INT.withName("bin_length"), JAVA_INT.withName("max_read_length"),
+            JAVA_LONG.withName("genome_length_haploid"), ADDRESS.withName("output_prefix"));
+
+    /** sp_build_model_args: argv of BuildModel.main, src/BuildModel.java:22-33 (an int after a pointer is followed by 4 bytes of padding). */
+    static final StructLayout BUILD_MODEL_ARGS = MemoryLayout.structLayout(
+            ADDRESS.withName("repeatmasker_file"), JAVA_INT.withName("repeatmasker_rows"), MemoryLayout.paddingLayout(4),
+            ADDRESS.withName("trf_file"), JAVA_INT.withName("trf_rows"), MemoryLayout.paddingLayout(4),
+            ADDRESS.withName("segdups_file"), JAVA_INT.withName("segdups_rows"), MemoryLayout.paddingLayout(4),
+            ADDRESS.withName("reference_fai"), ADDRESS.withName("reference_cytobands"), ADDRESS.withName("gnomad_vcf"),
+            JAVA_INT.withName("only_pass"), MemoryLayout.paddingLayout(4), ADDRESS.withName("output_dir"),
+            JAVA_INT.withName("verbose"), MemoryLayout.paddingLayout(4));
 
     /** The one deviation from the reference argv: the RNG seed (the reference uses `new Random()`). */
     static long seed() {
