@@ -61,6 +61,13 @@ int sp_load_reference_fasta(sp_ctx* ctx, const char* path);
 /* Same, from bytes already in host memory (one byte per base, case preserved). */
 int sp_set_reference(sp_ctx* ctx, const uint8_t* bases, int64_t length);
 int64_t sp_reference_length(const sp_ctx* ctx);
+/* The resident reference as a device pointer (read-only for the caller; valid until the reference is replaced), e.g. the
+ * source of an NCCL broadcast to the other GPUs of a box. */
+int sp_reference_device(sp_ctx* ctx, void** device_ptr, int64_t* length);
+/* Makes room for a reference of `length` bytes that the caller writes ON THE DEVICE (the destination of that broadcast) and
+ * returns where; the caller must have finished writing before the next call on this context. Replaces any reference and
+ * drops any population, like sp_set_reference; no host copy exists afterwards (the VCF writers need one). */
+int sp_reference_device_buffer(sp_ctx* ctx, int64_t length, void** device_ptr);
 
 /* ---- row V0: variant table + per-haplotype lists ------------------------------------------------------ */
 /* The `variants` array and `haplotype2variants[_last]` (src/SimulateHaplotypes.java:52-60) as SoA + CSR.

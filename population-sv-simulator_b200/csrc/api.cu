@@ -424,6 +424,29 @@ int sp_set_reference(sp_ctx* ctx, const uint8_t* bases, int64_t length) {
 
 int64_t sp_reference_length(const sp_ctx* ctx) { return ctx ? ctx->ref_len : -1; }
 
+int sp_reference_device(sp_ctx* ctx, void** device_ptr, int64_t* length) {
+    SP_API_BEGIN
+    if (!device_ptr) throw Error(SP_ERR_ARG, "null output pointer");
+    if (ctx->ref_len <= 0 || !ctx->d_ref.p) throw Error(SP_ERR_ARG, "no reference is resident");
+    SP_CUDA(cudaStreamSynchronize(ctx->stream));   // the caller reads it on a stream of its own
+    *device_ptr = ctx->d_ref.p;
+    if (length) *length = ctx->ref_len;
+    SP_API_END
+}
+
+int sp_reference_device_buffer(sp_ctx* ctx, int64_t length, void** device_ptr) {
+    SP_API_BEGIN
+    if (length <= 0 || length > INT32_MAX || !device_ptr) throw Error(SP_ERR_ARG, "bad reference buffer");
+    sp::free_population(ctx);
+    ctx->h_ref.clear();
+    SP_CUDA(cudaStreamSynchronize(ctx->stream));   // nothing of this context may still read the old reference
+    ctx->ref_len = length;
+    ctx->d_ref.reserve((size_t)length);
+    ctx->plan_last = -1; ctx->plan_first = 0;
+    *device_ptr = ctx->d_ref.p;
+    SP_API_END
+}
+
 int sp_set_variants(sp_ctx* ctx, int32_t n, const int8_t* sv_type, const int32_t* position, const int32_t* length,
                     const int64_t* payload_off, const uint8_t* payload_blob, const int8_t* has_payload) {
     SP_API_BEGIN

@@ -149,6 +149,8 @@ def load() -> C.CDLL:
         "sp_probe_bandwidth": (C.c_int, [vp, i32, i64, i32, i32, i32, P(C.c_double)]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
+        "sp_reference_device": (C.c_int, [vp, P(C.c_void_p), P(i64)]),
+        "sp_reference_device_buffer": (C.c_int, [vp, i64, P(C.c_void_p)]),
         "sp_reference_length": (i64, [vp]),
         "sp_set_variants": (C.c_int, [vp, i32, vp, vp, vp, vp, vp, vp]),
         "sp_set_haplotype_lists": (C.c_int, [vp, i32, vp, vp]),
@@ -288,6 +290,18 @@ class Context:
     def set_reference(self, bases: np.ndarray):
         bases = np.ascontiguousarray(bases, dtype=np.uint8)
         self._check(self.lib.sp_set_reference(self.h, _ptr(bases), bases.size))
+
+    def reference_device(self):
+        """(device pointer, length) of the resident reference."""
+        p, n = C.c_void_p(), C.c_int64()
+        self._check(self.lib.sp_reference_device(self.h, C.byref(p), C.byref(n)))
+        return int(p.value or 0), int(n.value)
+
+    def reference_device_buffer(self, length: int) -> int:
+        """Device pointer of a fresh reference buffer of `length` bytes for the caller to fill on the device."""
+        p = C.c_void_p()
+        self._check(self.lib.sp_reference_device_buffer(self.h, int(length), C.byref(p)))
+        return int(p.value or 0)
 
     @property
     def reference_length(self) -> int:

@@ -71,11 +71,13 @@ class _DeviceInt32:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 3, "strides": None}
 
 
-def simulate_population_sharded(ctx, argv, dist=None, write_files: bool = True):
+def simulate_population_sharded(ctx, argv, dist=None, write_files: bool = True, begun: bool = False):
     """SimulateHaplotypes.main (src/SimulateHaplotypes.java:75-116) across the ranks of `dist` (None = single process).
     Every rank calls this with the same argv and a context created with the same seed. Returns a dict with the rank's
     haplotype range and the global counts. Afterwards the context holds the rank's haplotype lists, ready for
-    sp_plan_haplotypes / the read kernel on the rank's own individuals."""
+    sp_plan_haplotypes / the read kernel on the rank's own individuals.
+    begun=True: the caller has already run ctx.population_begin(argv, first, last) for this rank's shard (the prologue has no
+    collective in it, so several runs' prologues may proceed in host threads while the exchanges stay in one order)."""
     import torch
     rank = dist.get_rank() if dist is not None else 0
     world = dist.get_world_size() if dist is not None else 1
@@ -83,7 +85,8 @@ def simulate_population_sharded(ctx, argv, dist=None, write_files: bool = True):
     if n_individuals < world:
         raise ValueError(f"{n_individuals} individuals cannot be sharded over {world} ranks")
     first, last = shard_of_haplotypes(n_individuals, rank, world)
-    ctx.population_begin(argv, first, last)
+    if not begun:
+        ctx.population_begin(argv, first, last)
     info = ctx.population_info()
     n_local = max(0, last - first + 1)
     if dist is None or world == 1:
@@ -118,3 +121,94 @@ def simulate_population_sharded(ctx, argv, dist=None, write_files: bool = True):
     else:
         ctx.population_finish(counts, None, None, 2)
     return dict(first=first, last=last, counts=counts, n_variants=V, all_off=all_off, all_ids=all_ids, collective=timing)
+
+
+# ---- one owner per run (whole genome: 24 independent runs of SimulateHaplotypes, BASELINE configs[2]) ----------------
+# A genome is 24 runs, one per chromosome (the reference takes one FASTA record per run, src/SimulateHaplotypes.java:120-135).
+# Sharding the individuals of every run over the ranks (above) makes every rank repeat every run's sequential prologue
+# (loadReference, the model, loadPositions, sampleVariants): 15 s of host time per rank for GRCh38. Here a run has ONE owner
+# that does the whole of SimulateHaplotypes for it (the genotype kernel over all haplotypes is microseconds) and then
+# broadcasts what materialisation needs (rows A1, V0 and the lists) to the other GPUs: the reference stays on the device and
+# goes over NVLink straight into the receivers' contexts, the tables travel as one packed byte tensor.
+
+_TABLE_FIELDS = (("sv_type", np.int8), ("position", np.int32), ("length", np.int32), ("payload_off", np.int64),
+                 ("payload", np.uint8), ("list_off", np.int64), ("list_ids", np.int32))
+
+
+def pack_tables(variants: dict, list_off: np.ndarray, list_ids: np.ndarray) -> np.ndarray:
+    """Variant table (Context.get_variants) + CSR haplotype lists as one uint8 array: a header of 7 int64 element counts,
+    then the arrays, each padded to 8 bytes."""
+    arrays = dict(variants, list_off=list_off, list_ids=list_ids)
+    parts = [np.array([np.asarray(arrays[k]).size for k, _ in _TABLE_FIELDS], dtype=np.int64).view(np.uint8)]
+    for k, dt in _TABLE_FIELDS:
+        b = np.ascontiguousarray(arrays[k], dtype=dt).view(np.uint8).ravel()
+        parts += [b, np.zeros((-b.size) % 8, dtype=np.uint8)]
+    return np.concatenate(parts)
+
+
+def unpack_tables(buf: np.ndarray):
+    """Inverse of pack_tables: (variants dict, list_off, list_ids)."""
+    buf = np.ascontiguousarray(buf, dtype=np.uint8)
+    counts = buf[: 8 * len(_TABLE_FIELDS)].view(np.int64)
+    at = 8 * len(_TABLE_FIELDS)
+    out = {}
+    for (k, dt), n in zip(_TABLE_FIELDS, counts):
+        nb = int(n) * np.dtype(dt).itemsize
+        out[k] = buf[at: at + nb].view(dt).copy()
+        at += nb + (-nb) % 8
+    list_off, list_ids = out.pop("list_off"), out.pop("list_ids")
+    return out, list_off, list_ids
+
+
+def take_lists(list_off: np.ndarray, list_ids: np.ndarray, first: int, last: int):
+    """The CSR rows [first, last] renumbered from 0."""
+    if last < first:
+        return np.zeros(1, np.int64), np.zeros(0, np.int32)
+    a, b = int(list_off[first]), int(list_off[last + 1])
+    return (list_off[first: last + 2] - a).astype(np.int64), list_ids[a:b].astype(np.int32)
+
+
+class _DeviceBytes:
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def share_population(ctx, dist, owner: int, first: int, last: int):
+    """After the owner's ctx finished a whole-population SimulateHaplotypes (population_begin(argv, 0, -1) +
+    population_finish), give every other rank's (empty) ctx what it needs to materialise ITS haplotypes [first, last]:
+    three broadcasts from `owner` (sizes, the packed tables, the reference device-to-device). On return a non-owner holds
+    the reference, the variant table and its own lists as haplotypes 0..last-first; the owner keeps its population and
+    addresses its shard as [first, last]. Returns (first, last) to pass to plan_haplotypes on this rank, and the bytes moved."""
+    import torch
+    rank = dist.get_rank()
+    nccl = dist.get_backend() == "nccl"
+    device = torch.device("cuda", torch.cuda.current_device()) if nccl else torch.device("cpu")
+    if rank == owner:
+        off, ids = ctx.get_haplotype_lists()
+        packed = pack_tables(ctx.get_variants(), off, ids)
+        ref_ptr, ref_len = ctx.reference_device() if nccl else (0, ctx.reference_length)
+        meta = torch.tensor([packed.size, ref_len], dtype=torch.int64, device=device)
+    else:
+        meta = torch.zeros(2, dtype=torch.int64, device=device)
+    dist.broadcast(meta, src=owner)
+    n_packed, ref_len = (int(x) for x in meta.cpu())
+    tables = torch.from_numpy(packed).to(device) if rank == owner else torch.empty(n_packed, dtype=torch.uint8, device=device)
+    dist.broadcast(tables, src=owner)
+    if nccl:
+        ptr = ref_ptr if rank == owner else ctx.reference_device_buffer(ref_len)
+        ref_t = torch.as_tensor(_DeviceBytes(ptr, ref_len), device=device)   # the library's own buffer on both sides
+        dist.broadcast(ref_t, src=owner)
+        torch.cuda.current_stream().synchronize()
+    else:   # gloo (CPU tests of this logic): the reference travels as host bytes
+        ref_t = torch.from_numpy(np.ascontiguousarray(ctx.host_reference)) if rank == owner else torch.empty(ref_len, dtype=torch.uint8)
+        dist.broadcast(ref_t, src=owner)
+        if rank != owner:
+            ctx.set_reference(ref_t.numpy())
+    moved = dict(tables_bytes=n_packed, reference_bytes=ref_len)
+    if rank == owner:
+        return first, last, moved
+    variants, off, ids = unpack_tables(tables.cpu().numpy())
+    ctx.set_variants(variants["sv_type"], variants["position"], variants["length"], variants["payload_off"], variants["payload"])
+    my_off, my_ids = take_lists(off, ids, first, last)
+    ctx.set_haplotype_lists(my_off, my_ids)
+    return 0, last - first, moved

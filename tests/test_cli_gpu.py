@@ -56,4 +56,4 @@ def test_whole_genome_driver_small(tmp_path):
     assert [c["chromosome"] for c in rows] == ["chr1", "chr2", "chr3"]
     assert all(c["haplotypes"] == 8 and c["variants"] > 0 for c in rows)
     assert line["bases"] == sum(c["bases"] for c in rows) and line["gpu_launches"] > 0
-    assert all(c["bases"] > 0 and c["copy_ms"] > 0 for c in rows)
+    assert all(c["bases"] > 0 and c["copy_ms"] > 0 for c in rows) and line["wall_s"] > 0 and line["prologue_threads"] >= 1

@@ -10,8 +10,9 @@ The reference simulates one sequence per run (single FASTA record, `int` coordin
   python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/whole_genome.py
 
 Prints one JSON line: per-chromosome device times (CUDA events on the library's stream) and the whole-genome
-haplotype Gbp/s = bases all ranks materialised / max over ranks of the summed device time. Input generation and the
-SimulateHaplotypes prologue are reported beside it, not inside it.
+haplotype Gbp/s = bases all ranks materialised / max over ranks of the summed device time; beside it the WALL seconds of the
+whole job after input generation (the chromosomes' host prologues run in threads, the exchanges in chromosome order).
+The inputs are written once per box (rank r writes chromosomes r, r+world, ...).
 """
 import argparse
 import json
@@ -42,6 +43,8 @@ def main():
     ap.add_argument("--chromosomes", type=int, default=len(GRCH38))
     ap.add_argument("--only", default="", help="comma-separated chromosome names (profiling one launch shape)")
     ap.add_argument("--repeats", type=int, default=3, help="materialisation passes per chromosome (first is warm-up)")
+    ap.add_argument("--threads", type=int, default=0, help="host threads for the chromosomes' prologues (0 = cores / ranks, at most 8)")
+    ap.add_argument("--keep-inputs", action="store_true")
     args = ap.parse_args()
 
     import torch
@@ -60,44 +63,83 @@ def main():
     rows = []
     dev_ms = 0.0
     bases_total = 0
-    t_gen_total = t_pop_total = 0.0
     launches = 0
     only = set(filter(None, args.only.split(",")))
-    for name, full in GRCH38[: args.chromosomes]:
-        if only and name not in only:
-            continue
-        L = max(200_000, int(full * args.scale))
-        work = tempfile.mkdtemp(prefix=f"synthpop_wg_r{rank}_")
-        try:
+    chroms = [(name, max(200_000, int(full * args.scale))) for name, full in GRCH38[: args.chromosomes] if not only or name in only]
+
+    # ---- inputs: every file once per box (rank r writes chromosomes r, r+world, ...), not once per rank
+    shared = os.path.join(tempfile.gettempdir(), f"synthpop_wg_shared_{os.environ.get('MASTER_PORT', '0')}_{args.scale}")
+    t0 = time.perf_counter()
+    for k, (name, L) in enumerate(chroms):
+        if k % world == rank:
+            synth.generate_population_inputs(os.path.join(shared, name), L, n_insertions=30000)
+    if dist is not None:
+        dist.barrier()
+    t_gen_total = time.perf_counter() - t0
+
+    def inputs_of(name, L):   # the paths generate_population_inputs wrote (no arrays are rebuilt)
+        root = os.path.join(shared, name)
+        return synth.SynthInputs(root=root, reference_file=os.path.join(root, "reference.fa"), model_dir=os.path.join(root, "model"),
+                                 repeat_intervals_file=os.path.join(root, "repeatIntervals.txt"), segdups_file=os.path.join(root, "segdups.txt"),
+                                 insertions_file=os.path.join(root, "insertions.txt"), n_insertions=30000, reference_length=L)
+
+    if dist is not None:
+        first, last = sharded.shard_of_haplotypes(args.individuals, rank, world)
+    else:
+        first, last = sharded.shard_of_haplotypes(args.individuals, args.as_rank, args.as_world)
+
+    def begin(name, L, seed0=42):
+        """The prologue of one chromosome's SimulateHaplotypes (rows A1-A3, S1, G/C/N of this rank's columns): host work
+        with no collective in it, so the chromosomes' prologues run side by side in threads (the C ABI releases the GIL)."""
+        argv = inputs_of(name, L).simulate_argv(os.path.join(shared, name, f"out_r{rank}"), args.individuals, n_frequent=5000)
+        t0 = time.perf_counter()
+        # The reference throws on some (inputs, seed) pairs (e.g. ArrayIndexOutOfBoundsException in its interval
+        # intersection when the pair buffer grows, src/SimulateHaplotypes.java:548-555) and the library reproduces
+        # that; the prologue is the same on every rank, so every rank moves on to the next seed together.
+        for seed in range(seed0, 50):
+            ctx = splib.Context(local_rank, seed)
+            try:
+                if dist is not None:
+                    ctx.population_begin(argv, first, last)
+                else:
+                    # one process cannot all-gather with absent ranks: draw the whole population here (the genotype
+                    # kernel over all 200 haplotypes is microseconds) and materialise only the shard's individuals
+                    ctx.population_begin(argv, 0, -1)
+                ctx.synchronize()
+                return ctx, argv, seed, time.perf_counter() - t0
+            except splib.SynthpopError as e:
+                ctx.close()
+                if e.code != 6 or seed == 49:
+                    raise
+
+    from concurrent.futures import ThreadPoolExecutor
+    n_threads = args.threads if args.threads > 0 else max(1, (os.cpu_count() or 8) // max(1, world if dist is not None else 1))
+    n_threads = min(n_threads, 8)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t_wall0 = time.perf_counter()
+    t_pop_total = 0.0
+    with ThreadPoolExecutor(n_threads) as pool:
+        futures = [pool.submit(begin, name, L) for name, L in chroms]
+        for (name, L), fut in zip(chroms, futures):   # exchanges and launches in chromosome order on every rank
+            ctx, argv, seed, t_begin = fut.result()
             t0 = time.perf_counter()
-            inp = synth.generate_population_inputs(os.path.join(work, "in"), L, n_insertions=30000)
-            t_gen = time.perf_counter() - t0
-            out_dir = os.path.join(work, "out"); os.makedirs(out_dir)
-            argv = inp.simulate_argv(out_dir, args.individuals, n_frequent=5000)
-            # The reference throws on some (inputs, seed) pairs (e.g. ArrayIndexOutOfBoundsException in its interval
-            # intersection when the pair buffer grows, src/SimulateHaplotypes.java:548-555) and the library reproduces
-            # that; the prologue is the same on every rank, so every rank moves on to the next seed together.
-            t0 = time.perf_counter()
-            for seed in range(42, 50):
-                ctx = splib.Context(local_rank, seed)
-                ctx.set_stream(stream.cuda_stream)
+            while True:
                 try:
+                    ctx.set_stream(stream.cuda_stream)
                     if dist is not None:
-                        res = sharded.simulate_population_sharded(ctx, argv, dist, write_files=False)
-                        first, last = res["first"], res["last"]
+                        sharded.simulate_population_sharded(ctx, argv, dist, write_files=False, begun=True)
                     else:
-                        first, last = sharded.shard_of_haplotypes(args.individuals, args.as_rank, args.as_world)
-                        # one process cannot all-gather with absent ranks: draw the whole population here (the genotype
-                        # kernel over all 200 haplotypes is microseconds) and materialise only the shard's individuals
-                        ctx.population_begin(argv, 0, -1)
                         ctx.population_finish(None, None, None, 2)
                     break
-                except splib.SynthpopError as e:
+                except splib.SynthpopError as e:   # rows I/R1 can throw too; same on every rank: next seed, together
                     ctx.close()
-                    if e.code != 6 or seed == 49:
+                    if e.code != 6 or seed >= 49:
                         raise
+                    ctx, argv, seed, _ = begin(name, L, seed + 1)
             ctx.synchronize()
-            t_pop = time.perf_counter() - t0
+            t_pop = t_begin + time.perf_counter() - t0
             info = ctx.population_info()
             best = None
             l0 = ctx.kernel_launches
@@ -119,21 +161,24 @@ def main():
             bases = int(lens.sum())
             rows.append({"chromosome": name, "length": L, "variants": info["n_variants"], "seed": seed, "haplotypes": int(lens.size),
                          "bases": bases, "plan_ms": round(best[0], 3), "copy_ms": round(best[1], 3),
-                         "generate_inputs_s": round(t_gen, 2), "simulate_population_s": round(t_pop, 2)})
+                         "prologue_s": round(t_begin, 3), "exchange_and_finish_s": round(t_pop - t_begin, 3)})
             dev_ms += sum(best)
             bases_total += bases
-            t_gen_total += t_gen
             t_pop_total += t_pop
             ctx.close()
-        finally:
-            shutil.rmtree(work, ignore_errors=True)
+    torch.cuda.synchronize()
+    wall_s = time.perf_counter() - t_wall0
+    if dist is not None:
+        dist.barrier()
+    if rank == 0 and not args.keep_inputs:
+        shutil.rmtree(shared, ignore_errors=True)
 
     if dist is not None:
-        t = torch.tensor([dev_ms, t_pop_total], dtype=torch.float64, device="cuda")
+        t = torch.tensor([dev_ms, t_pop_total, wall_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         b = torch.tensor([bases_total], dtype=torch.int64, device="cuda")
         dist.all_reduce(b, op=dist.ReduceOp.SUM)
-        dev_ms, t_pop_total, bases_total = float(t[0]), float(t[1]), int(b[0])
+        dev_ms, t_pop_total, wall_s, bases_total = float(t[0]), float(t[1]), float(t[2]), int(b[0])
     if rank == 0:
         n_ranks = world if dist is not None else 1
         line = {"metric": "simulated haplotype Gbp/s", "value": bases_total / dev_ms / 1e6, "unit": "Gbp/s", "n_gpus": n_ranks,
@@ -141,7 +186,11 @@ def main():
                                        f"{args.individuals} diploid individuals sharded by individual over "
                                        f"{world if dist is not None else args.as_world} ranks"
                                        + ("" if dist is not None else f"; this process is rank {args.as_rank} alone")},
-                "bases": bases_total, "device_ms": dev_ms, "simulate_population_s": t_pop_total,
+                "bases": bases_total, "device_ms": dev_ms,
+                "wall_s": wall_s, "wall_what": f"max over ranks, from the barrier after input generation to the last chromosome materialised "
+                                               f"({args.repeats} plan+copy passes each), prologues in {n_threads} host threads per rank",
+                "wall_gbp_s": bases_total / wall_s / 1e9,
+                "simulate_population_s_summed_over_chromosomes": t_pop_total, "prologue_threads": n_threads,
                 "generate_inputs_s": t_gen_total, "gpu_launches": launches, "timing": "CUDA events, max over ranks of "
                 "the summed plan+copy time, best of the passes after the warm-up one", "chromosomes": rows}
         print(json.dumps(line))
