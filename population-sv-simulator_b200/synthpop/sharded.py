@@ -206,8 +206,10 @@ def share_population(ctx, dist, owner: int, first: int, last: int):
             ctx.set_reference(ref_t.numpy())
     moved = dict(tables_bytes=n_packed, reference_bytes=ref_len)
     if rank == owner:
+        moved["n_variants"] = int(packed[:8].view(np.int64)[0])
         return first, last, moved
     variants, off, ids = unpack_tables(tables.cpu().numpy())
+    moved["n_variants"] = int(variants["sv_type"].size)
     ctx.set_variants(variants["sv_type"], variants["position"], variants["length"], variants["payload_off"], variants["payload"])
     my_off, my_ids = take_lists(off, ids, first, last)
     ctx.set_haplotype_lists(my_off, my_ids)

@@ -18,6 +18,30 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     hap_dir, argv = sys.argv[1], sys.argv[2:]
     ctx = lib.Context(local_rank, 42)
+    if os.environ.get("SYNTHPOP_TEST_OWNER_MODE"):
+        # one owner (the LAST rank) runs the whole of SimulateHaplotypes and writes its files; the others receive the
+        # reference and the tables (sharded.share_population) and materialise their own individuals
+        rank, world = dist.get_rank(), dist.get_world_size()
+        owner = world - 1
+        first, last = sharded.shard_of_haplotypes(int(argv[9]), rank, world)
+        if rank == owner:
+            ctx.simulate_haplotypes(argv)
+        f, l, moved = sharded.share_population(ctx, dist, owner, first, last)
+        assert moved["reference_bytes"] > 0 and moved["n_variants"] > 0
+        lens, stride = ctx.plan_haplotypes(f, l, True)
+        ctx.materialise()
+        for h in range(first, last + 1):
+            data = ctx.copy_haplotype(f + (h - first), stride).tobytes()
+            if rank != owner:   # a receiver numbers its haplotypes from 0: the FASTA header says so too
+                head, _, rest = data.partition(b"\n")
+                assert head == b">chr1_%d" % (f + (h - first))
+                data = b">chr1_%d\n" % h + rest
+            with open(os.path.join(hap_dir, f"haplotype_{h}.fa"), "wb") as fh:
+                fh.write(data)
+        dist.barrier()
+        ctx.close()
+        dist.destroy_process_group()
+        return
     res = sharded.simulate_population_sharded(ctx, argv, dist)
     # each rank materialises its own haplotypes from the lists still resident on its GPU
     first, last = res["first"], res["last"]

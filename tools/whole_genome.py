@@ -45,6 +45,9 @@ def main():
     ap.add_argument("--repeats", type=int, default=3, help="materialisation passes per chromosome (first is warm-up)")
     ap.add_argument("--threads", type=int, default=0, help="host threads for the chromosomes' prologues (0 = cores / ranks, at most 8)")
     ap.add_argument("--keep-inputs", action="store_true")
+    ap.add_argument("--mode", choices=("owner", "sharded"), default="owner",
+                    help="multi-rank runs: 'owner' = each chromosome's SimulateHaplotypes runs on one rank, which broadcasts the reference "
+                         "and the tables (sharded.share_population); 'sharded' = every rank runs every prologue on its own columns")
     args = ap.parse_args()
 
     import torch
@@ -120,52 +123,120 @@ def main():
     torch.cuda.synchronize()
     t_wall0 = time.perf_counter()
     t_pop_total = 0.0
-    with ThreadPoolExecutor(n_threads) as pool:
-        futures = [pool.submit(begin, name, L) for name, L in chroms]
-        for (name, L), fut in zip(chroms, futures):   # exchanges and launches in chromosome order on every rank
-            ctx, argv, seed, t_begin = fut.result()
-            t0 = time.perf_counter()
-            while True:
-                try:
+    owner_mode = dist is not None and args.mode == "owner"
+
+    def begin_whole(name, L):
+        """Owner mode: the whole of SimulateHaplotypes for one chromosome on this rank (all haplotypes, no files)."""
+        argv = inputs_of(name, L).simulate_argv(os.path.join(shared, name, f"out_r{rank}"), args.individuals, n_frequent=5000)
+        t0 = time.perf_counter()
+        for seed in range(42, 50):
+            ctx = splib.Context(local_rank, seed)
+            try:
+                ctx.population_begin(argv, 0, -1)
+                ctx.population_finish(None, None, None, 2)
+                ctx.synchronize()
+                return ctx, argv, seed, time.perf_counter() - t0
+            except splib.SynthpopError as e:
+                ctx.close()
+                if e.code != 6 or seed == 49:
+                    raise
+
+    def materialise_passes(ctx, f, l):
+        best = None
+        for it in range(args.repeats):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            with torch.cuda.stream(stream):
+                ev[0].record(stream)
+                lens, stride = ctx.plan_haplotypes(f, l, False)
+                ev[1].record(stream)
+                ctx.materialise()
+                ev[2].record(stream)
+            torch.cuda.synchronize()
+            t = (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]))
+            if it > 0 or args.repeats == 1:
+                best = t if best is None or sum(t) < sum(best) else best
+        return best, lens, stride
+
+    moved_bytes = 0
+    if owner_mode:
+        recv = splib.Context(local_rank, 42)   # one receiving context for all the chromosomes this rank does not own
+        recv.set_stream(stream.cuda_stream)
+        with ThreadPoolExecutor(n_threads) as pool:
+            futures = {k: pool.submit(begin_whole, name, L) for k, (name, L) in enumerate(chroms) if k % world == rank}
+            for k, (name, L) in enumerate(chroms):   # broadcasts and launches in chromosome order on every rank
+                owner = k % world
+                t_begin, seed = 0.0, -1
+                t0 = time.perf_counter()
+                if owner == rank:
+                    ctx, argv, seed, t_begin = futures[k].result()
+                    t0 = time.perf_counter()
                     ctx.set_stream(stream.cuda_stream)
-                    if dist is not None:
-                        sharded.simulate_population_sharded(ctx, argv, dist, write_files=False, begun=True)
-                    else:
-                        ctx.population_finish(None, None, None, 2)
-                    break
-                except splib.SynthpopError as e:   # rows I/R1 can throw too; same on every rank: next seed, together
+                else:
+                    ctx = recv
+                f, l, moved = sharded.share_population(ctx, dist, owner, first, last)
+                moved_bytes += moved["tables_bytes"] + moved["reference_bytes"]
+                t_share = time.perf_counter() - t0
+                l0 = ctx.kernel_launches
+                best, lens, stride = materialise_passes(ctx, f, l)
+                launches += (ctx.kernel_launches - l0) // args.repeats
+                assert lens.size == last - first + 1 and int(lens.min()) > 0 and stride >= int(lens.max())
+                bases = int(lens.sum())
+                rows.append({"chromosome": name, "length": L, "variants": moved["n_variants"], "owner": owner, "seed": seed, "haplotypes": int(lens.size),
+                             "bases": bases, "plan_ms": round(best[0], 3), "copy_ms": round(best[1], 3),
+                             "prologue_s": round(t_begin, 3), "share_s": round(t_share, 3)})
+                dev_ms += sum(best)
+                bases_total += bases
+                t_pop_total += t_begin + t_share
+                if owner == rank:
                     ctx.close()
-                    if e.code != 6 or seed >= 49:
-                        raise
-                    ctx, argv, seed, _ = begin(name, L, seed + 1)
-            ctx.synchronize()
-            t_pop = t_begin + time.perf_counter() - t0
-            info = ctx.population_info()
-            best = None
-            l0 = ctx.kernel_launches
-            for it in range(args.repeats):
-                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-                with torch.cuda.stream(stream):
-                    ev[0].record(stream)
-                    lens, stride = ctx.plan_haplotypes(first, last, False)
-                    ev[1].record(stream)
-                    ctx.materialise()
-                    ev[2].record(stream)
-                torch.cuda.synchronize()
-                t = (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]))
-                if it > 0 or args.repeats == 1:
-                    best = t if best is None or sum(t) < sum(best) else best
-            launches += (ctx.kernel_launches - l0) // args.repeats
-            # size-independent property: every haplotype is the reference plus its own net edit, and differs from it
-            assert lens.size == last - first + 1 and int(lens.min()) > 0 and stride >= int(lens.max())
-            bases = int(lens.sum())
-            rows.append({"chromosome": name, "length": L, "variants": info["n_variants"], "seed": seed, "haplotypes": int(lens.size),
-                         "bases": bases, "plan_ms": round(best[0], 3), "copy_ms": round(best[1], 3),
-                         "prologue_s": round(t_begin, 3), "exchange_and_finish_s": round(t_pop - t_begin, 3)})
-            dev_ms += sum(best)
-            bases_total += bases
-            t_pop_total += t_pop
-            ctx.close()
+        recv.close()
+    else:
+        with ThreadPoolExecutor(n_threads) as pool:
+            futures = [pool.submit(begin, name, L) for name, L in chroms]
+            for (name, L), fut in zip(chroms, futures):   # exchanges and launches in chromosome order on every rank
+                ctx, argv, seed, t_begin = fut.result()
+                t0 = time.perf_counter()
+                while True:
+                    try:
+                        ctx.set_stream(stream.cuda_stream)
+                        if dist is not None:
+                            sharded.simulate_population_sharded(ctx, argv, dist, write_files=False, begun=True)
+                        else:
+                            ctx.population_finish(None, None, None, 2)
+                        break
+                    except splib.SynthpopError as e:   # rows I/R1 can throw too; same on every rank: next seed, together
+                        ctx.close()
+                        if e.code != 6 or seed >= 49:
+                            raise
+                        ctx, argv, seed, _ = begin(name, L, seed + 1)
+                ctx.synchronize()
+                t_pop = t_begin + time.perf_counter() - t0
+                info = ctx.population_info()
+                best = None
+                l0 = ctx.kernel_launches
+                for it in range(args.repeats):
+                    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                    with torch.cuda.stream(stream):
+                        ev[0].record(stream)
+                        lens, stride = ctx.plan_haplotypes(first, last, False)
+                        ev[1].record(stream)
+                        ctx.materialise()
+                        ev[2].record(stream)
+                    torch.cuda.synchronize()
+                    t = (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]))
+                    if it > 0 or args.repeats == 1:
+                        best = t if best is None or sum(t) < sum(best) else best
+                launches += (ctx.kernel_launches - l0) // args.repeats
+                # size-independent property: every haplotype is the reference plus its own net edit, and differs from it
+                assert lens.size == last - first + 1 and int(lens.min()) > 0 and stride >= int(lens.max())
+                bases = int(lens.sum())
+                rows.append({"chromosome": name, "length": L, "variants": info["n_variants"], "seed": seed, "haplotypes": int(lens.size),
+                             "bases": bases, "plan_ms": round(best[0], 3), "copy_ms": round(best[1], 3),
+                             "prologue_s": round(t_begin, 3), "exchange_and_finish_s": round(t_pop - t_begin, 3)})
+                dev_ms += sum(best)
+                bases_total += bases
+                t_pop_total += t_pop
+                ctx.close()
     torch.cuda.synchronize()
     wall_s = time.perf_counter() - t_wall0
     if dist is not None:
@@ -191,6 +262,7 @@ def main():
                                                f"({args.repeats} plan+copy passes each), prologues in {n_threads} host threads per rank",
                 "wall_gbp_s": bases_total / wall_s / 1e9,
                 "simulate_population_s_summed_over_chromosomes": t_pop_total, "prologue_threads": n_threads,
+                "mode": ("owner" if owner_mode else "sharded"), "broadcast_bytes_per_rank": moved_bytes,
                 "generate_inputs_s": t_gen_total, "gpu_launches": launches, "timing": "CUDA events, max over ranks of "
                 "the summed plan+copy time, best of the passes after the warm-up one", "chromosomes": rows}
         print(json.dumps(line))
