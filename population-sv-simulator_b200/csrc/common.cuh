@@ -96,7 +96,7 @@ struct sp_ctx {
     // The plan (segment scan, tile table) of a batch is issued on the same second stream, into the plan set the copy kernel
     // of the batch before is NOT reading, so the host round trip that sizes the slots never waits behind a copy kernel.
     cudaStream_t pop_stream = nullptr;
-    cudaEvent_t ev_planned = nullptr;   // recorded on the planning stream after tile_table_kernel of the current plan
+    cudaEvent_t ev_planned = nullptr;   // recorded on the planning stream after tile_runs_kernel of the current plan
     std::string err;
     int64_t launches = 0;
     int sm_count = 148;
