@@ -577,6 +577,8 @@ def main():
     import torch
     from synthpop import lib as splib, synth, sharded
 
+    # cores (and, by first touch, pinned host buffers) on the GPU's NUMA node: the e2e leg's D2H streams must not cross sockets
+    bound_cores = sharded.bind_rank_to_gpu(local_rank) if os.environ.get("SYNTHPOP_NO_BIND") is None else 0
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -827,7 +829,8 @@ def main():
                              "note": "rows A1-A3, S1, I, R1 are the replicated sequential prologue (host); G/C/N is the device part over all 1000 haplotypes"},
                 "e2e": {"value": float(e2e_val[0]), "unit": "Gbp/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "haplotypes_per_call": ne, "d2h_peak_GBps_measured": d2h_peak,
-                        "frac_of_d2h_peak": (float(e2e_val[0]) / world / d2h_peak) if d2h_peak else None},
+                        "frac_of_d2h_peak": (float(e2e_val[0]) / world / d2h_peak) if d2h_peak else None,
+                        "cores_bound_to_gpu_numa_node_rank0": bound_cores},
                 "clocks": sampler.summary(), "wall_s_timed_region": t_wall}
         if reads_obj is not None:
             line["reads"] = reads_obj

@@ -214,3 +214,26 @@ def share_population(ctx, dist, owner: int, first: int, last: int):
     my_off, my_ids = take_lists(off, ids, first, last)
     ctx.set_haplotype_lists(my_off, my_ids)
     return 0, last - first, moved
+
+
+def bind_rank_to_gpu(local_rank: int):
+    """Pin this process to the CPU cores the driver reports as local to its GPU (NVML cpu affinity), so that pinned host
+    buffers allocated afterwards are on the GPU's NUMA node and the D2H streams of the ranks of one box do not cross sockets.
+    Returns the number of cores bound, or 0 when NVML is not usable (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        index = int(visible.split(",")[local_rank]) if visible and visible.split(",")[local_rank].isdigit() else local_rank
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        allowed = os.sched_getaffinity(0)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1} & allowed
+        if not cpus or cpus == allowed:
+            return 0
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return 0

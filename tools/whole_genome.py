@@ -56,6 +56,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    sharded.bind_rank_to_gpu(local_rank)
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
