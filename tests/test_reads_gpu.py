@@ -134,16 +134,21 @@ def test_reads_from_a_materialised_haplotype_never_leave_the_device(sp, oracle_l
         ctx.set_reference(case["ref"])
         ctx.set_variants(case["sv_type"], case["position"], case["length"], case["payload_off"], case["payload"])
         ctx.set_haplotype_lists(case["list_off"], case["ids"])
-        ctx.plan_haplotypes(0, 1, False)
+        lens, stride = ctx.plan_haplotypes(0, 1, False)
         ctx.materialise()
         _configure(sp, ctx, p, 21, model, False, sp.READS_PER_READ_STREAMS)
         for h in range(2):
             hap = oh.build_haplotype(oracle_lib, case["ref"], case["sv_type"], case["position"], case["length"],
                                      case["payload_off"], case["payload"], None, case["lists"][h])
+            assert ctx.copy_haplotype(h, stride).tobytes() == hap.tobytes(), ("haplotype", h, int(lens[h]), hap.size)
             want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)
             res = ctx.reads_simulate_haplotype(h, ref_num=h + 1)
             got = ctx.reads_copy(res["file_bytes"])
-            assert res["n_reads"] == log["n_reads"], (h, res, log["n_reads"])
+            if res["n_reads"] != log["n_reads"]:   # seen once in ten full-suite runs: say which side moved
+                again = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)[1]["n_reads"]
+                res2 = ctx.reads_simulate_haplotype(h, ref_num=h + 1)
+                raise AssertionError((h, "device", res, "device again", res2, "oracle", log["n_reads"], "oracle again", again,
+                                      "haplotype bytes", hap.size, "model bytes", os.path.getsize(model), p))
             assert got.size == want.size, (h, got.size, want.size, res)
             bad = np.nonzero(got != want)[0]
             assert bad.size == 0, (h, int(bad[0]), int(bad.size), got[max(0, bad[0] - 30):bad[0] + 30].tobytes(), want[max(0, bad[0] - 30):bad[0] + 30].tobytes())
