@@ -97,6 +97,22 @@ int sp_synchronize(sp_ctx* ctx);
 int sp_haplotype_device(sp_ctx* ctx, int32_t h, void** device_ptr, int64_t* sequence_length);
 /* D2H of the framed bytes of haplotype h. */
 int sp_copy_haplotype(sp_ctx* ctx, int32_t h, uint8_t* host_out, int64_t capacity, int64_t* written);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). ONE haplotype, through the same plan and
+ * copy kernels as sp_plan_haplotypes + sp_materialise, with every plan table in a file-scope device array of
+ * about 3.1 MB (csrc/materialise.cu, `static __device__ __align__(256)`; every GPU that loads the library holds it until
+ * exit). The call allocates nothing: no cudaMalloc, cudaFree or allocating library routine. Inputs: the reference and the
+ * variant table resident in the context (sp_set_reference / sp_load_reference_fasta, sp_set_variants) and the haplotype's
+ * edit list as n_ids ascending variant ids in DEVICE memory. Output: the haplotype's bases (no FASTA framing) into the
+ * caller's 16-byte aligned DEVICE buffer of `capacity` bytes; *length = bytes written (set even when capacity is too small).
+ * Limits: n_ids <= SP_STATIC_MAX_EDITS and a haplotype of at most SP_STATIC_MAX_OUTPUT_BYTES bytes, beyond which the call
+ * fails with SP_ERR_ARG and a message naming the limit. Runs on the context's stream and returns after it has drained.
+ * The array is shared by every context of the process on that GPU and keeps the last call's contents (what must start at
+ * zero is cleared per call): calls that overlap on the GPU race — serialise them. */
+#define SP_STATIC_MAX_EDITS 16384
+#define SP_STATIC_MAX_OUTPUT_BYTES (512ll << 20)
+int sp_materialise_haplotype_static(sp_ctx* ctx, const int32_t* device_ids, int32_t n_ids, void* device_out, int64_t capacity,
+                                    int64_t* length);
 /* plan + materialise + D2H of all of [first..last] into one host buffer, back to back (offsets: n+1 entries). */
 int sp_build_haplotypes_host(sp_ctx* ctx, int32_t first, int32_t last, int32_t fasta_framing, uint8_t* host_out,
                              int64_t capacity, int64_t* offsets);

@@ -443,4 +443,118 @@ void launch_tiled_copy(sp_ctx* c, const uint8_t* src, const uint8_t* payload, co
     SP_CUDA(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------------------------------------- no-allocation variant
+// sp_materialise_haplotype_static: one haplotype through the same plan_kernel / tile_runs_kernel / materialise_kernel, with
+// every plan table (segment offsets, per-tile counts, tile descriptors, run array, the scan's temporary storage) in ONE
+// file-scope device array instead of the context's cudaMalloc'ed buffers. For callers that may not allocate (CUDA graph
+// capture, serving loops). Every GPU that loads the library holds the array until exit; every call shares it (calls that
+// overlap on the GPU race) and it keeps the last call's contents, so the words that must start at zero are cleared per call.
+constexpr int32_t STATIC_MAX_EDITS = SP_STATIC_MAX_EDITS;
+constexpr int64_t STATIC_MAX_TILES = SP_STATIC_MAX_OUTPUT_BYTES / TILE_BYTES;
+constexpr int64_t STATIC_NSEG = 3 * (int64_t)STATIC_MAX_EDITS + 5;
+constexpr size_t static_up(size_t x) { return (x + 255) / 256 * 256; }
+// header (256 B): int64 list_off[2] @0, seg_base[2] @16, aux_off[2] @32, hap_len @48; int32 err[4] @64; aux bytes @128 ('\n' + slack)
+constexpr size_t ST_HDR = 0;
+constexpr size_t ST_SEG_DST = 256;
+constexpr size_t ST_SEG_SRC = ST_SEG_DST + static_up(STATIC_NSEG * 8);
+constexpr size_t ST_TILE_S0 = ST_SEG_SRC + static_up(STATIC_NSEG * 8);
+constexpr size_t ST_TILE_MORE = ST_TILE_S0 + static_up(STATIC_MAX_TILES * 4);
+constexpr size_t ST_TILE_SCAN = ST_TILE_MORE + static_up((STATIC_MAX_TILES + 1) * 4);
+constexpr size_t ST_DESC = ST_TILE_SCAN + static_up((STATIC_MAX_TILES + 1) * 4);
+constexpr size_t ST_ITEMS = ST_DESC + static_up(STATIC_MAX_TILES * sizeof(TileDesc));
+constexpr size_t ST_CUB = ST_ITEMS + static_up((STATIC_NSEG + STATIC_MAX_TILES + 64) * sizeof(RunItem));
+constexpr size_t ST_CUB_BYTES = 64 << 10;
+constexpr size_t ST_BYTES = ST_CUB + ST_CUB_BYTES;   // about 3.1 MB
+static_assert(ST_BYTES <= (4u << 20), "the static scratch is meant to stay modest");
+
+static __device__ __align__(256) uint8_t g_static_scratch[ST_BYTES];
+
+// In host code `g_static_scratch` is a stand-in, not a device address: the address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static uint8_t* static_scratch_address(int device) {
+    static uint8_t* addr[64] = {};
+    static bool known[64] = {};
+    if (device < 0 || device >= 64) throw Error(SP_ERR_ARG, "static scratch: device index out of range");
+    if (!known[device]) {
+        void* p = nullptr;
+        SP_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) throw Error(SP_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        addr[device] = (uint8_t*)p;
+        known[device] = true;
+    }
+    return addr[device];
+}
+
+__global__ void static_plan_init_kernel(uint8_t* __restrict__ s, int32_t n_ids) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int64_t* h = (int64_t*)s;
+    h[0] = 0; h[1] = n_ids;                       // list_off of the one haplotype
+    h[2] = 0; h[3] = 3 * (int64_t)n_ids + 5;      // seg_base
+    h[4] = 1; h[5] = 1;                           // aux_off: no FASTA header (the '\n' of bw.newLine sits at aux[0])
+    h[6] = 0;                                     // hap_len
+    int32_t* e = (int32_t*)(s + 64);
+    e[0] = e[1] = e[2] = e[3] = 0;                // the plan's error words must start at zero
+    s[128] = (uint8_t)'\n';
+}
+
+void materialise_haplotype_static(sp_ctx* c, const int32_t* device_ids, int32_t n_ids, void* device_out, int64_t capacity, int64_t* length) {
+    if (c->ref_len <= 0 || !c->d_ref.p) throw Error(SP_ERR_ARG, "no reference loaded");
+    if (n_ids < 0 || (n_ids > 0 && !device_ids)) throw Error(SP_ERR_ARG, "bad edit list");
+    if (n_ids > 0 && c->n_variants <= 0) throw Error(SP_ERR_ARG, "no variant table loaded");
+    if (n_ids > STATIC_MAX_EDITS)
+        throw Error(SP_ERR_ARG, "sp_materialise_haplotype_static: " + std::to_string(n_ids) + " edits exceed the static scratch (SP_STATIC_MAX_EDITS = " +
+                                    std::to_string(STATIC_MAX_EDITS) + "); use sp_plan_haplotypes + sp_materialise");
+    if (!device_out || capacity <= 0 || ((uintptr_t)device_out & 15u)) throw Error(SP_ERR_ARG, "the output must be a 16-byte aligned device buffer");
+    uint8_t* s = static_scratch_address(c->device);
+    cudaStream_t st = c->stream;
+    int64_t* hdr = (int64_t*)(s + ST_HDR);
+    int64_t* seg_dst = (int64_t*)(s + ST_SEG_DST);
+    int64_t* seg_src = (int64_t*)(s + ST_SEG_SRC);
+    static_plan_init_kernel<<<1, 32, 0, st>>>(s, n_ids);
+    plan_kernel<<<1, 256, 0, st>>>(c->d_type.p, c->d_pos.p, c->d_len.p, c->d_payload_off.p, c->n_variants, hdr + 0, device_ids, c->ref_len, 0,
+                                   hdr + 4, hdr + 2, seg_dst, seg_src, hdr + 6, (int32_t*)(s + 64));
+    c->launches += 2;
+    SP_CUDA(cudaGetLastError());
+    int64_t h_len = 0;
+    int32_t h_err[4] = {0, 0, 0, 0};
+    SP_CUDA(cudaMemcpyAsync(&h_len, hdr + 6, 8, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaMemcpyAsync(h_err, s + 64, 16, cudaMemcpyDeviceToHost, st));
+    SP_CUDA(cudaStreamSynchronize(st));
+    if (h_err[0] != 0) {
+        static const char* what[] = {"", "ArrayIndexOutOfBoundsException: variant id", "IndexOutOfBoundsException: start > end",
+                                     "IndexOutOfBoundsException: end > reference length", "invalid svType"};
+        throw Error(h_err[0] == 4 ? SP_ERR_ARG : SP_ERR_JAVA_EXCEPTION, std::string(what[h_err[0]]) + " (list index " + std::to_string(h_err[2]) + ")");
+    }
+    if (length) *length = h_len;
+    if (h_len > (int64_t)SP_STATIC_MAX_OUTPUT_BYTES)
+        throw Error(SP_ERR_ARG, "sp_materialise_haplotype_static: a haplotype of " + std::to_string(h_len) + " bytes exceeds the static scratch (SP_STATIC_MAX_OUTPUT_BYTES = " +
+                                    std::to_string((int64_t)SP_STATIC_MAX_OUTPUT_BYTES) + ")");
+    if (h_len > capacity) throw Error(SP_ERR_ARG, "device buffer too small: the haplotype has " + std::to_string(h_len) + " bytes");
+    const int64_t tiles = round_up(std::max<int64_t>(h_len, 1), TILE_BYTES) / TILE_BYTES;
+    int32_t* s0 = (int32_t*)(s + ST_TILE_S0);
+    int32_t* more = (int32_t*)(s + ST_TILE_MORE);
+    int32_t* scan = (int32_t*)(s + ST_TILE_SCAN);
+    TileDesc* desc = (TileDesc*)(s + ST_DESC);
+    RunItem* items = (RunItem*)(s + ST_ITEMS);
+    size_t tmp = 0;
+    SP_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, more, scan, (int)tiles, st));   // size query: allocates nothing
+    if (tmp > ST_CUB_BYTES) throw Error(SP_ERR, "static scratch: the scan needs " + std::to_string(tmp) + " bytes of temporary storage");
+    const unsigned grid = (unsigned)((tiles + 255) / 256);
+    tile_runs_kernel<false><<<grid, 256, 0, st>>>(seg_dst, seg_src, hdr + 2, 1, tiles, s0, more, nullptr, nullptr, nullptr);
+    tmp = ST_CUB_BYTES;
+    SP_CUDA(cub::DeviceScan::ExclusiveSum(s + ST_CUB, tmp, more, scan, (int)tiles, st));
+    tile_runs_kernel<true><<<grid, 256, 0, st>>>(seg_dst, seg_src, hdr + 2, 1, tiles, s0, nullptr, scan, desc, items);
+    launch_materialise(st, tiles, c->d_ref.p, c->d_payload.p, s + 128, desc, items, (uint8_t*)device_out, tiles * TILE_BYTES, tiles, 1);
+    c->launches += 4;
+    SP_CUDA(cudaGetLastError());
+    SP_CUDA(cudaStreamSynchronize(st));   // the output is complete and the scratch is free again when the call returns
+}
+
 }  // namespace sp
+
+extern "C" int sp_materialise_haplotype_static(sp_ctx* ctx, const int32_t* device_ids, int32_t n_ids, void* device_out, int64_t capacity,
+                                               int64_t* length) {
+    SP_API_BEGIN
+    sp::materialise_haplotype_static(ctx, device_ids, n_ids, device_out, capacity, length);
+    SP_API_END
+}

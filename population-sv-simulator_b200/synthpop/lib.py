@@ -149,6 +149,7 @@ def load() -> C.CDLL:
         "sp_probe_bandwidth": (C.c_int, [vp, i32, i64, i32, i32, i32, P(C.c_double)]),
         "sp_load_reference_fasta": (C.c_int, [vp, cp]),
         "sp_set_reference": (C.c_int, [vp, vp, i64]),
+        "sp_materialise_haplotype_static": (C.c_int, [vp, vp, i32, vp, i64, P(i64)]),
         "sp_reference_device": (C.c_int, [vp, P(C.c_void_p), P(i64)]),
         "sp_reference_device_buffer": (C.c_int, [vp, i64, P(C.c_void_p)]),
         "sp_reference_length": (i64, [vp]),
@@ -364,6 +365,14 @@ class Context:
         n = C.c_int64()
         self._check(self.lib.sp_haplotype_device(self.h, h, C.byref(p), C.byref(n)))
         return int(p.value or 0), int(n.value)
+
+    def materialise_haplotype_static(self, device_ids: int, n_ids: int, device_out: int, capacity: int) -> int:
+        """sp_materialise_haplotype_static: one haplotype from a DEVICE edit list into a DEVICE buffer, no allocation (plan
+        tables in the library's static device array). Pointers are integers (e.g. tensor.data_ptr()). Returns the length."""
+        n = C.c_int64(0)
+        self._check(self.lib.sp_materialise_haplotype_static(self.h, C.c_void_p(device_ids or 0), int(n_ids), C.c_void_p(device_out or 0),
+                                                             int(capacity), C.byref(n)))
+        return int(n.value)
 
     def copy_haplotype(self, h: int, capacity: int) -> np.ndarray:
         out = np.empty(capacity, dtype=np.uint8)
