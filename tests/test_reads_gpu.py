@@ -144,11 +144,19 @@ def test_reads_from_a_materialised_haplotype_never_leave_the_device(sp, oracle_l
             want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)
             res = ctx.reads_simulate_haplotype(h, ref_num=h + 1)
             got = ctx.reads_copy(res["file_bytes"])
-            if res["n_reads"] != log["n_reads"]:   # seen once in ten full-suite runs: say which side moved
-                again = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)[1]["n_reads"]
-                res2 = ctx.reads_simulate_haplotype(h, ref_num=h + 1)
-                raise AssertionError((h, "device", res, "device again", res2, "oracle", log["n_reads"], "oracle again", again,
-                                      "haplotype bytes", hap.size, "model bytes", os.path.getsize(model), p))
+            if res["n_reads"] != log["n_reads"] or got.size != want.size:
+                # Seen in about one of ten full-suite runs, never alone: the FIRST in-process oracle call of this test returned
+                # a different read count than the same call repeated (and than the oracle run standalone, which agrees with the
+                # device). The oracle is recomputed twice; the test goes on only if both repeats agree with each other, and says so.
+                import warnings
+                first = (log["n_reads"], want.size)
+                want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)
+                want3, log3 = oh.pbsim_simulate(oracle_lib, hap, model, seed=21, per_read_streams=True, ref_num=h + 1, **p)
+                details = (h, "device", res, "oracle first call", first, "oracle repeated", (log["n_reads"], want.size), (log3["n_reads"], want3.size),
+                           "haplotype bytes", hap.size, "model bytes", os.path.getsize(model), p)
+                assert want.tobytes() == want3.tobytes() and (log["n_reads"], want.size) != first, details
+                warnings.warn(f"oracle pbsim call was not repeatable in this process: {details}")
+            assert res["n_reads"] == log["n_reads"], (h, res, log["n_reads"])
             assert got.size == want.size, (h, got.size, want.size, res)
             bad = np.nonzero(got != want)[0]
             assert bad.size == 0, (h, int(bad[0]), int(bad.size), got[max(0, bad[0] - 30):bad[0] + 30].tobytes(), want[max(0, bad[0] - 30):bad[0] + 30].tobytes())
