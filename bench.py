@@ -99,24 +99,30 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
     n_ind = n_haps // 2
     tot = dict(bases=0, reads=0, dropped=0, k_ms=0.0, p_ms=0.0, mix_copy_ms=0.0, mix_order_ms=0.0, mixed_bytes=0, mixed_reads=0)
     used = last = None
+    one_by_one_ms = []
 
-    def individual(h0, timed):
+    def individual(h0, timed, pair=True):
         nonlocal used, last
         if resample:
             ctx.population_genotypes(h0, h0 + 1)   # rows G/C/N for this individual
         ctx.plan_haplotypes(h0, h0 + 1, False)
         ctx.materialise()
         ctx.reads_mix_begin()
-        for h in (h0, h0 + 1):
-            r = ctx.reads_simulate_haplotype(h, 1)
-            tm = ctx.reads_timing()
+        if pair:
+            # both read kernels of the individual in flight (sp_reads_mix_add_pair): the kernel time is the device span from
+            # the first kernel's start to the second one's end
+            res, span = ctx.reads_mix_add_pair(h0, h0 + 1, 1, 1)
             if timed:
-                tot["bases"] += r["bases"]; tot["reads"] += r["n_reads"]; tot["dropped"] += r["n_dropped"]
-                tot["k_ms"] += tm["kernel_ms"]; tot["p_ms"] += tm["plan_ms"]
+                for r in res:
+                    tot["bases"] += r["bases"]; tot["reads"] += r["n_reads"]; tot["dropped"] += r["n_dropped"]
+                tot["k_ms"] += span; tot["p_ms"] += ctx.reads_timing()["plan_ms"]
+        else:   # warm-up: one by one (also what the draw statistics are taken from)
+            for h in (h0, h0 + 1):
+                r = ctx.reads_simulate_haplotype(h, 1)
                 last = r
-                if h == first_hap + 2 * n_ind - 1:
-                    _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of the last haplotype's reads
-            ctx.reads_mix_add()
+                _, _, used = ctx.reads_log(r["n_reads"])   # rand() calls of this haplotype's reads
+                one_by_one_ms.append(ctx.reads_timing()["kernel_ms"])
+                ctx.reads_mix_add()
         n_mixed, mixed_bytes = ctx.reads_mix_finish(42 + h0)
         if timed:
             mt = ctx.reads_mix_timing()
@@ -124,7 +130,8 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
             tot["mixed_bytes"] += mixed_bytes; tot["mixed_reads"] += n_mixed
         return n_mixed, mixed_bytes
 
-    individual(first_hap, False)   # warm-up: allocations, table upload, the three buffer sets the mix rotates
+    individual(first_hap, False, pair=False)   # warm-up: allocations, table upload, the three buffer sets the mix rotates
+    individual(first_hap, False, pair=True)    # and the second batch state of the pair path
     torch.cuda.synchronize()
     l0 = ctx.kernel_launches
     t0 = time.perf_counter()
@@ -153,10 +160,12 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
     return {"metric": "CCS read Gbp/s", "value": bases / dt / 1e9, "unit": "Gbp/s",
             "workload": f"pbsim2 model mode, {depth}x over {2 * n_ind} materialised chr1-sized haplotypes ({n_ind} individuals, mixed per individual), "
                         f"length 15000+-2000 in [5000,30000], accuracy-mean 0.995, 6:50:54, synthetic 5-state HMM quality model ({quality} emission centres), per-read glibc streams",
-            "timed": "per individual: genotype kernels, plan, materialisation, two read launches, mix; wall clock around all individuals",
+            "timed": "per individual: genotype kernels, plan, materialisation, two read launches in flight together, mix; wall clock around all individuals",
             "draws_per_base": round(draws_per_base, 2),
             "reads": tot["reads"], "dropped_NNNNN": tot["dropped"], "bases": bases, "wall_s": dt, "kernel_ms": k_ms, "host_plan_ms": tot["p_ms"],
             "kernel_gbp_s": bases / (k_ms / 1e3) / 1e9, "gpu_launches": ctx.kernel_launches - l0,
+            "kernel_ms_what": "per individual, the span of its two read kernels in flight together (sp_reads_mix_add_pair)",
+            "one_by_one_kernel_ms_warmup_individual": one_by_one_ms,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": 22.3 * bases, "traffic_source": "22.3 B per base, ncu of one launch (profiles/r02a_reads_kernel_base_raw.csv)",
                          "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE},

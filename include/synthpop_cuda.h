@@ -258,6 +258,14 @@ int sp_trio_add_child(sp_ctx* ctx, int32_t father_individual, int32_t mother_ind
  * written in ascending key order. */
 int sp_reads_mix_begin(sp_ctx* ctx);
 int sp_reads_mix_add(sp_ctx* ctx);
+/* docker/haplotype2reads.sh:53-58 for both haplotypes of an individual in one call: the pbsim runs of planned haplotypes h0
+ * (ID1) and h1 (ID2) with BOTH read kernels in flight (the second one's CTAs fill the thinning tail of the first), then both
+ * batches added to the mix in that order; equivalent to sp_reads_simulate_haplotype(h0) + sp_reads_mix_add +
+ * sp_reads_simulate_haplotype(h1) + sp_reads_mix_add, record for record. Per-read streams only. seed_per_haplotype != 0:
+ * haplotype h is sequenced with sp_haplotype_read_seed(configured seed, h), as sp_haplotype2reads does. The four outputs are arrays
+ * of 2 (may be NULL); kernels_span_ms = first kernel's start to second kernel's end on the device. */
+int sp_reads_mix_add_pair(sp_ctx* ctx, int32_t h0, int32_t h1, int64_t ref_num0, int64_t ref_num1, int32_t seed_per_haplotype,
+                          int64_t* n_reads, int64_t* file_bytes, int64_t* n_dropped, int64_t* bases, double* kernels_span_ms);
 int sp_reads_mix_finish(sp_ctx* ctx, int64_t shuffle_seed, int64_t* n_reads, int64_t* file_bytes);
 /* The 1x chunks of docker/reads2svs.sh:65-74 (N_ROWS_1X = N_ROWS / MAX_COVERAGE, rounded up to a multiple of 4;
  * `split -d -l`) and the coverage sweep of :98-128 (coverage c = the first c chunks): rows per chunk, rows and bytes

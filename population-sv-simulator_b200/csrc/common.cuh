@@ -173,6 +173,7 @@ struct sp_ctx {
 
     // row P: read simulation (pbsim2 model mode)
     sp::ReadState* reads = nullptr;
+    sp::ReadState* reads_b = nullptr;   // the second batch in flight of sp_reads_mix_add_pair (same configuration and tables)
 
     // row D: SampleReadsFromLengthBins
     sp::LengthBinState* bins = nullptr;

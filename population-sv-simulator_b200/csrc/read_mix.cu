@@ -130,9 +130,12 @@ static void mix_begin(sp_ctx* c) {
 
 // Takes the device records of the last sp_reads_simulate_* call (no copy: the buffers change owner).
 static void mix_add(sp_ctx* c) {
-    ReadMixState& M = mix_of(c);
     if (!c->reads || !c->reads->configured) throw Error(SP_ERR_ARG, "sp_reads_configure has not been called");
-    ReadState& R = *c->reads;
+    mix_add_from(c, *c->reads);
+}
+
+void mix_add_from(sp_ctx* c, ReadState& R) {
+    ReadMixState& M = mix_of(c);
     if (M.n_sources >= 2) throw Error(SP_ERR_ARG, "read mix: an individual has two haplotypes");
     MixSource& S = M.src[M.n_sources++];
     S.records.swap(R.d_out); S.dropped.swap(R.d_dropped); S.rec_off.swap(R.d_rec_off);
@@ -310,13 +313,8 @@ int sp_haplotype2reads(sp_ctx* ctx, int32_t id1, int64_t shuffle_seed, const cha
     if (rc == SP_OK) rc = sp_materialise(ctx);
     if (rc == SP_OK) rc = sp_reads_mix_begin(ctx);
     if (rc == SP_OK && (!ctx->reads || !ctx->reads->configured)) throw Error(SP_ERR_ARG, "sp_reads_configure has not been called");
-    const uint32_t seed0 = rc == SP_OK ? ctx->reads->par.seed : 0;
-    for (int h = id1; h <= id1 + 1 && rc == SP_OK; h++) {
-        ctx->reads->par.seed = sp_haplotype_read_seed(seed0, h);
-        rc = sp_reads_simulate_haplotype(ctx, h, 1, nullptr, nullptr, nullptr, nullptr);
-        ctx->reads->par.seed = seed0;
-        if (rc == SP_OK) rc = sp_reads_mix_add(ctx);
-    }
+    // one pbsim run per haplotype, each with its own seed (sp_haplotype_read_seed), both read kernels in flight
+    if (rc == SP_OK) rc = sp_reads_mix_add_pair(ctx, id1, id1 + 1, 1, 1, 1, nullptr, nullptr, nullptr, nullptr, nullptr);
     if (rc == SP_OK) rc = sp_reads_mix_finish(ctx, shuffle_seed, n_reads, file_bytes);
     if (rc != SP_OK) return rc;
     if (output_file) {   // device -> pinned ring -> file, the writer thread overlapping the copies (csrc/file_sink.h)

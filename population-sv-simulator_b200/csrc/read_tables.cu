@@ -335,12 +335,21 @@ void reads_configure(sp_ctx* c, const sp_read_args* a) {
     R.n_reads = 0;
     R.configured = true;
     R.plan_tables_stale = true;
+    static uint64_t epoch = 0;
+    R.config_epoch = ++epoch;
 }
 
 void free_reads(sp_ctx* c) {
-    if (c->reads && c->reads->ev0) { cudaEventDestroy(c->reads->ev0); cudaEventDestroy(c->reads->ev1); }
-    delete c->reads;
-    c->reads = nullptr;
+    for (ReadState** pr : {&c->reads, &c->reads_b}) {
+        ReadState* r = *pr;
+        if (!r) continue;
+        if (r->kernel_stream) { cudaStreamSynchronize(r->kernel_stream); cudaStreamDestroy(r->kernel_stream); }
+        if (r->ev0) { cudaEventDestroy(r->ev0); cudaEventDestroy(r->ev1); }
+        if (r->ev_ready) cudaEventDestroy(r->ev_ready);
+        if (r->h_ctr) cudaFreeHost(r->h_ctr);
+        delete r;
+        *pr = nullptr;
+    }
 }
 
 }  // namespace sp

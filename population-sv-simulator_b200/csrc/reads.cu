@@ -618,8 +618,10 @@ static void ensure_host_plan(sp_ctx* c, ReadState& R) {
 
 // simulate_by_model's loop header and per-read plan (:1641-1655, :1682, :2282) for every read of one sequence, then the
 // read kernel. d_seq must stay valid until the stream has run the kernel.
-static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64_t ref_num) {
-    ReadState& R = reads_of(c);
+// One batch (= all reads of one sequence) in three phases, so that two batches can be in flight (simulate_pair below):
+// plan_batch (the per-read plan; synchronises the context's stream), launch_batch (the read kernel on stream ks, nothing
+// waits), collect_batch (waits for ks, reads the counters). simulate_on_device is the three in a row on the context's stream.
+static bool plan_batch(sp_ctx* c, ReadState& R, const uint8_t* d_seq, int64_t L, int64_t ref_num) {
     const ReadParams& p = R.par;
     const ReadTablesHost& t = R.tab;
     cudaStream_t st = c->stream;
@@ -646,7 +648,7 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
         R.d_out.reserve((size_t)R.out_bytes + 64, 0.05);
         SP_CUDA(cudaMemsetAsync(R.d_ctr.p, 0, 64, st));
         R.n_dropped = 0;
-        if (n_reads == 0) return;
+        if (n_reads == 0) return false;
     } else {
         R.plan_on_device = false;
         long long len_total = 0;
@@ -721,7 +723,7 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
         SP_CUDA(cudaMemcpyAsync(R.d_rec_off.p, R.h_rec_off.data(), (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
         SP_CUDA(cudaMemsetAsync(R.d_ctr.p, 0, 64, st));
         R.n_dropped = 0;
-        if (n_reads == 0) return;
+        if (n_reads == 0) return false;
 
         // group the reads so that the 32 threads of a warp run nearly the same trip counts: longest first (tail balance),
         // then by accuracy class (same tables, similar deletion loops). Counting sort, O(n).
@@ -737,6 +739,16 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
             SP_CUDA(cudaMemcpyAsync(R.d_order.p, R.h_order.data(), n_reads * 4, cudaMemcpyHostToDevice, st));
         }
     }
+    R.cur_seq = d_seq; R.cur_L = L; R.cur_max_len = max_len; R.cur_replay = replay;
+    R.plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_plan0).count();
+    return true;
+}
+
+static void launch_batch(sp_ctx* c, ReadState& R, cudaStream_t ks) {
+    const ReadParams& p = R.par;
+    const bool replay = R.cur_replay;
+    const int64_t n_reads = R.n_reads, ref_num = R.ref_num;
+    const std::string id = ">" + p.id_prefix + std::to_string(ref_num) + "_";
     int ctas_per_sm = 1;
     {   // Shared memory against L1: the generator state columns are 17 KB per CTA, but the table walks, the template
         // chunks and the scratch words live in L1. Measured at 30x chr1: the driver's default split (5 CTAs per SM, large
@@ -750,13 +762,14 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     if (const char* e = getenv("SYNTHPOP_READS_CTAS_PER_SM")) ctas_per_sm = std::max(1, std::min(ctas_per_sm, atoi(e)));  // tuning hook
     const int64_t want_ctas = (n_reads + RD_THREADS - 1) / RD_THREADS;
     const int64_t grid_full = std::min<int64_t>(want_ctas, (int64_t)c->sm_count * ctas_per_sm);
-    const int64_t words = ((int64_t)max_len + 3) / 4 + 1;
+    const int64_t words = ((int64_t)R.cur_max_len + 3) / 4 + 1;
     const size_t cta_scratch = (size_t)(RD_THREADS / 32) * 2 * words * 32 * sizeof(uint32_t);
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(grid_full, (int64_t)((16ull << 30) / cta_scratch)));  // <= 16 GiB of scratch
     R.d_scratch.reserve(cta_scratch * grid, 0.0);
+    if (!R.h_ctr) SP_CUDA(cudaHostAlloc((void**)&R.h_ctr, 8 * sizeof(unsigned long long), cudaHostAllocDefault));
 
     ReadJob J{};
-    J.seq = d_seq; J.L = L; J.n_reads = n_reads; J.order = R.d_order.p;
+    J.seq = R.cur_seq; J.L = R.cur_L; J.n_reads = n_reads; J.order = R.d_order.p;
     J.len = R.d_len.p; J.acc = R.d_acc.p; J.ndel = R.d_ndel.p; J.rec_off = R.d_rec_off.p;
     J.seed = p.seed; J.ref_num = ref_num; J.no_error = p.no_error ? 1 : 0;
     J.replay = replay ? R.d_replay.p : nullptr;
@@ -767,18 +780,21 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     if (id.size() >= sizeof J.id) throw Error(SP_ERR_ARG, "read id prefix too long");
     memcpy(J.id, id.data(), id.size());
     J.id_len = (int32_t)id.size();
-    R.plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_plan0).count();
     if (!R.ev0) { SP_CUDA(cudaEventCreate(&R.ev0)); SP_CUDA(cudaEventCreate(&R.ev1)); }
-    SP_CUDA(cudaEventRecord(R.ev0, st));
-    if (replay) reads_kernel<true><<<grid, RD_THREADS, 0, st>>>(J, R.dev);
-    else reads_kernel<false><<<grid, RD_THREADS, 0, st>>>(J, R.dev);
+    SP_CUDA(cudaEventRecord(R.ev0, ks));
+    if (replay) reads_kernel<true><<<grid, RD_THREADS, 0, ks>>>(J, R.dev);
+    else reads_kernel<false><<<grid, RD_THREADS, 0, ks>>>(J, R.dev);
     c->launches++;
     SP_CUDA(cudaGetLastError());
-    SP_CUDA(cudaEventRecord(R.ev1, st));
-    unsigned long long ctr[8];
-    SP_CUDA(cudaMemcpyAsync(ctr, R.d_ctr.p, sizeof ctr, cudaMemcpyDeviceToHost, st));
-    SP_CUDA(cudaStreamSynchronize(st));
+    SP_CUDA(cudaEventRecord(R.ev1, ks));
+    SP_CUDA(cudaMemcpyAsync(R.h_ctr, R.d_ctr.p, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ks));   // pinned: does not wait
+}
+
+static void collect_batch(sp_ctx* c, ReadState& R, cudaStream_t ks) {
+    SP_CUDA(cudaStreamSynchronize(ks));
     SP_CUDA(cudaEventElapsedTime(&R.kernel_ms, R.ev0, R.ev1));
+    const unsigned long long* ctr = R.h_ctr;
+    if (R.cur_replay) R.have_replay = false;
     if (ctr[1] != 0) {
         static const char* what[] = {"", "a read of length 1 (the reference computes rand() % 0)",
                                      "a read at least as long as the sequence it is drawn from (unsupported: the reference truncates it)",
@@ -787,7 +803,74 @@ static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64
     }
     R.n_dropped = (int64_t)ctr[3];
     R.out_bytes -= (int64_t)ctr[4];
-    if (replay) R.have_replay = false;
+}
+
+static void simulate_on_device(sp_ctx* c, const uint8_t* d_seq, int64_t L, int64_t ref_num) {
+    ReadState& R = reads_of(c);
+    if (!plan_batch(c, R, d_seq, L, ref_num)) return;
+    launch_batch(c, R, c->stream);
+    collect_batch(c, R, c->stream);
+}
+
+// The same configuration on a second set of batch buffers. The device tables are shared (read-only); the host tables are
+// copied because the plan reads them.
+static ReadState& second_state(sp_ctx* c) {
+    ReadState& A = reads_of(c);
+    if (!c->reads_b) c->reads_b = new ReadState();
+    ReadState& B = *c->reads_b;
+    if (B.config_epoch != A.config_epoch) {
+        B.par = A.par; B.tab = A.tab; B.dev = A.dev;
+        B.have_replay = false; B.n_reads = 0; B.plan_tables_stale = true; B.configured = true;
+        B.config_epoch = A.config_epoch;
+    }
+    if (!B.kernel_stream) SP_CUDA(cudaStreamCreateWithFlags(&B.kernel_stream, cudaStreamNonBlocking));
+    if (!B.ev_ready) SP_CUDA(cudaEventCreateWithFlags(&B.ev_ready, cudaEventDisableTiming));
+    return B;
+}
+
+// docker/haplotype2reads.sh:53-58 sequences haplotype ID1, then ID2, then concatenates. Here both read kernels are in flight:
+// a launch is one persistent wave of CTAs that fetch reads until none is left, so its last third runs with fewer and fewer
+// warps (35 of 40 resident on average, profiles/r02a_reads_kernel_base_raw.csv); the second haplotype's CTAs take the slots
+// the first one's give up. Reads are independent of each other (per-read streams), so every record is what the one-by-one
+// calls produce. Both batches become sources of the mix, in order.
+static void simulate_pair_into_mix(sp_ctx* c, const uint8_t* seq0, int64_t L0, int64_t ref_num0, const uint8_t* seq1, int64_t L1,
+                                   int64_t ref_num1, const uint32_t* seeds /*[2] or null: the configured seed for both*/, int64_t* n_reads,
+                                   int64_t* file_bytes, int64_t* n_dropped, int64_t* bases, double* span_ms) {
+    ReadState& A = reads_of(c);
+    if (A.par.stream_mode == SP_READS_REPLAY) throw Error(SP_ERR_ARG, "sp_reads_mix_add_pair: per-read streams only (a replay log belongs to one sequence)");
+    ReadState& B = second_state(c);
+    struct SeedGuard {   // the configured seed comes back whatever happens below
+        ReadState &A, &B; uint32_t seed;
+        ~SeedGuard() { A.par.seed = seed; B.par.seed = seed; }
+    } guard{A, B, A.par.seed};
+    if (seeds) { A.par.seed = seeds[0]; B.par.seed = seeds[1]; }
+    const bool a = plan_batch(c, A, seq0, L0, ref_num0);
+    const bool b = plan_batch(c, B, seq1, L1, ref_num1);
+    SP_CUDA(cudaEventRecord(B.ev_ready, c->stream));              // both plans (and whatever made the sequences) are done
+    SP_CUDA(cudaStreamWaitEvent(B.kernel_stream, B.ev_ready, 0));
+    if (a) launch_batch(c, A, c->stream);
+    if (b) launch_batch(c, B, B.kernel_stream);
+    try {
+        if (a) collect_batch(c, A, c->stream);
+    } catch (...) {
+        cudaStreamSynchronize(B.kernel_stream);   // nothing of this call is still running when the error leaves
+        throw;
+    }
+    if (b) collect_batch(c, B, B.kernel_stream);
+    A.pair_span_ms = 0.f;
+    if (a && b) SP_CUDA(cudaEventElapsedTime(&A.pair_span_ms, A.ev0, B.ev1));
+    else if (a) A.pair_span_ms = A.kernel_ms;
+    else if (b) A.pair_span_ms = B.kernel_ms;
+    ReadState* r[2] = {&A, &B};
+    for (int k = 0; k < 2; k++) {
+        if (n_reads) n_reads[k] = r[k]->n_reads;
+        if (file_bytes) file_bytes[k] = r[k]->out_bytes;
+        if (n_dropped) n_dropped[k] = r[k]->n_dropped;
+        if (bases) bases[k] = r[k]->emitted_bases;
+    }
+    if (span_ms) *span_ms = A.pair_span_ms;
+    mix_add_from(c, A);
+    mix_add_from(c, B);
 }
 
 static void fetch_read_log(sp_ctx* c, ReadState& R) {
@@ -899,6 +982,26 @@ int sp_reads_simulate_haplotype(sp_ctx* ctx, int32_t h, int64_t ref_num, int64_t
     if (rc != SP_OK) return rc;
     sp::simulate_on_device(ctx, (const uint8_t*)p, L, ref_num);
     report(sp::reads_of(ctx), n_reads, file_bytes, n_dropped, bases);
+    SP_API_END
+}
+
+int sp_reads_mix_add_pair(sp_ctx* ctx, int32_t h0, int32_t h1, int64_t ref_num0, int64_t ref_num1, int32_t seed_per_haplotype,
+                          int64_t* n_reads, int64_t* file_bytes, int64_t* n_dropped, int64_t* bases, double* kernels_span_ms) {
+    SP_API_BEGIN
+    void *p0 = nullptr, *p1 = nullptr;
+    int64_t L0 = 0, L1 = 0;
+    if (!ctx->materialised) throw Error(SP_ERR_ARG, "sp_materialise has not been called");
+    int rc = sp_haplotype_device(ctx, h0, &p0, &L0);
+    if (rc != SP_OK) return rc;
+    rc = sp_haplotype_device(ctx, h1, &p1, &L1);
+    if (rc != SP_OK) return rc;
+    uint32_t seeds[2] = {0, 0};
+    if (seed_per_haplotype) {
+        const uint32_t seed0 = sp::reads_of(ctx).par.seed;
+        seeds[0] = sp_haplotype_read_seed(seed0, h0); seeds[1] = sp_haplotype_read_seed(seed0, h1);
+    }
+    sp::simulate_pair_into_mix(ctx, (const uint8_t*)p0, L0, ref_num0, (const uint8_t*)p1, L1, ref_num1, seed_per_haplotype ? seeds : nullptr,
+                               n_reads, file_bytes, n_dropped, bases, kernels_span_ms);
     SP_API_END
 }
 

@@ -95,10 +95,22 @@ struct ReadState {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float kernel_ms = 0.f;
     double plan_ms = 0.0;
+    // what launch_batch / collect_batch need of the batch plan_batch made (reads.cu)
+    const uint8_t* cur_seq = nullptr;
+    int64_t cur_L = 0;
+    int32_t cur_max_len = 2;
+    bool cur_replay = false;
+    unsigned long long* h_ctr = nullptr;    // pinned copy of d_ctr: the read-back does not wait for the kernel
+    uint64_t config_epoch = 0;              // bumped by sp_reads_configure: the second state follows the first
+    cudaStream_t kernel_stream = nullptr;   // second state only (sp_reads_mix_add_pair): the stream its kernel runs on
+    cudaEvent_t ev_ready = nullptr;         // second state only: the context's stream has finished both plans
+    float pair_span_ms = 0.f;               // first kernel's start to second kernel's end of the last pair
 };
 
 void reads_configure(sp_ctx* c, const sp_read_args* a);
 void reads_build_tables(ReadState& R);
 void free_reads(sp_ctx* c);
+// read_mix.cu: the records of R's last batch become the next source of the mix (the buffers change owner)
+void mix_add_from(sp_ctx* c, ReadState& R);
 
 }  // namespace sp

@@ -136,6 +136,7 @@ def load() -> C.CDLL:
         "sp_trio_add_child": (C.c_int, [vp, i32, i32, i64, i32, vp, vp, vp]),
         "sp_reads_mix_begin": (C.c_int, [vp]),
         "sp_reads_mix_add": (C.c_int, [vp]),
+        "sp_reads_mix_add_pair": (C.c_int, [vp, i32, i32, i64, i64, i32, P(i64), P(i64), P(i64), P(i64), P(C.c_double)]),
         "sp_reads_mix_finish": (C.c_int, [vp, i64, vp, vp]),
         "sp_reads_mix_coverage_prefix": (C.c_int, [vp, i32, i32, vp, vp, vp]),
         "sp_reads_mix_copy": (C.c_int, [vp, i64, i64, vp]),
@@ -473,6 +474,14 @@ class Context:
 
     def reads_mix_add(self):
         self._check(self.lib.sp_reads_mix_add(self.h))
+
+    def reads_mix_add_pair(self, h0: int, h1: int, ref_num0: int = 1, ref_num1: int = 1, seed_per_haplotype: bool = False):
+        """Both haplotypes of an individual sequenced with both read kernels in flight, then added to the mix (h0 first).
+        Returns a list of two result dicts (as reads_simulate_haplotype) and the device span of the two kernels in ms."""
+        n = (C.c_int64 * 2)(); fb = (C.c_int64 * 2)(); nd = (C.c_int64 * 2)(); nb = (C.c_int64 * 2)()
+        span = C.c_double()
+        self._check(self.lib.sp_reads_mix_add_pair(self.h, h0, h1, ref_num0, ref_num1, int(seed_per_haplotype), n, fb, nd, nb, C.byref(span)))
+        return [dict(n_reads=n[k], file_bytes=fb[k], n_dropped=nd[k], bases=nb[k]) for k in range(2)], span.value
 
     def reads_mix_finish(self, shuffle_seed: int):
         n, b = C.c_int64(), C.c_int64()

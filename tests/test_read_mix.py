@@ -124,3 +124,58 @@ def test_haplotype2reads_whole_script(sp, oracle_lib, tmp_path):
         files.append(want.tobytes())
     assert open(out, "rb").read() == rm.mix_reads(files, 77)
     assert files[0][:4000] != files[1][:4000] and sp.haplotype_read_seed(21, 0) != sp.haplotype_read_seed(21, 1)
+
+
+@pytest.mark.gpu
+def test_pair_in_flight_equals_one_by_one(sp, tmp_path):
+    """sp_reads_mix_add_pair (both read kernels of an individual in flight, second state and stream) against the one-by-one
+    calls, which the tests above pin to the oracle: same statistics per haplotype, same mixed file, twice in a row."""
+    from synthpop import synth
+    import test_reads_gpu as trg
+    rng = np.random.default_rng(9)
+    case = oh.random_edit_lists(rng, 500_000, 250, 4, max_len=3000)
+    model = str(tmp_path / "hmm.model"); synth.write_hmm_model(model)
+    p = dict(CCS, depth=4.0)
+    with sp.Context(0, 42) as ctx:
+        ctx.set_reference(case["ref"])
+        ctx.set_variants(case["sv_type"], case["position"], case["length"], case["payload_off"], case["payload"])
+        ctx.set_haplotype_lists(case["list_off"], case["ids"])
+        trg._configure(sp, ctx, p, 33, model, False, sp.READS_PER_READ_STREAMS)
+        ctx.plan_haplotypes(0, 3, False)
+        ctx.materialise()
+        for h0 in (2, 0, 2):
+            ctx.reads_mix_begin()
+            one = []
+            for h in (h0, h0 + 1):
+                one.append(ctx.reads_simulate_haplotype(h, ref_num=1))
+                ctx.reads_mix_add()
+            n, nbytes = ctx.reads_mix_finish(5 + h0)
+            want = ctx.reads_mix_copy(0, nbytes).tobytes()
+            ctx.reads_mix_begin()
+            l0 = ctx.kernel_launches
+            res, span = ctx.reads_mix_add_pair(h0, h0 + 1, 1, 1)
+            assert span > 0 and ctx.kernel_launches > l0
+            for a, b in zip(one, res):
+                assert {k: a[k] for k in b} == b
+            n2, b2 = ctx.reads_mix_finish(5 + h0)
+            assert (n2, b2) == (n, nbytes)
+            assert ctx.reads_mix_copy(0, b2).tobytes() == want
+        # per-haplotype seeds change the reads (and sp_haplotype2reads, which is pinned to the oracle above, runs this path)
+        ctx.reads_mix_begin()
+        res2, _ = ctx.reads_mix_add_pair(2, 3, 1, 1, seed_per_haplotype=True)
+        n3, b3 = ctx.reads_mix_finish(7)
+        assert ctx.reads_mix_copy(0, b3).tobytes() != want
+        # a reconfiguration reaches the second state too
+        trg._configure(sp, ctx, dict(p, depth=2.0), 34, model, False, sp.READS_PER_READ_STREAMS)
+        ctx.reads_mix_begin()
+        one = []
+        for h in (0, 1):
+            one.append(ctx.reads_simulate_haplotype(h, ref_num=1))
+            ctx.reads_mix_add()
+        n, nbytes = ctx.reads_mix_finish(1)
+        want = ctx.reads_mix_copy(0, nbytes).tobytes()
+        ctx.reads_mix_begin()
+        res, _ = ctx.reads_mix_add_pair(0, 1, 1, 1)
+        assert [r["n_reads"] for r in res] == [r["n_reads"] for r in one]
+        n2, b2 = ctx.reads_mix_finish(1)
+        assert ctx.reads_mix_copy(0, b2).tobytes() == want
