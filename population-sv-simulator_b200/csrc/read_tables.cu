@@ -255,10 +255,9 @@ void reads_build_tables(ReadState& R) {
 }
 
 // set_sim_param + the option checks of main (docker/pbsim2.cpp:217-389, :1047-1107). Errors carry pbsim's messages.
-void reads_configure(sp_ctx* c, const sp_read_args* a) {
+// Host half only (parameters + tables, no device): what tests/emu links to run the kernel's per-read code on the CPU.
+void reads_set_params(ReadState& R, const sp_read_args* a) {
     if (!a) throw Error(SP_ERR_ARG, "null sp_read_args");
-    if (!c->reads) c->reads = new ReadState();
-    ReadState& R = *c->reads;
     R.configured = false;
     ReadParams p;
     const int FASTQ_LEN_MAX = 1000000;
@@ -299,6 +298,13 @@ void reads_configure(sp_ctx* c, const sp_read_args* a) {
     p.stream_mode = a->stream_mode;
     R.par = p;
     reads_build_tables(R);
+}
+
+void reads_configure(sp_ctx* c, const sp_read_args* a) {
+    if (!a) throw Error(SP_ERR_ARG, "null sp_read_args");
+    if (!c->reads) c->reads = new ReadState();
+    ReadState& R = *c->reads;
+    reads_set_params(R, a);
 
     // one device blob
     const ReadTablesHost& t = R.tab;

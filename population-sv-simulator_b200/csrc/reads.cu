@@ -23,57 +23,13 @@
 // Replay mode feeds the same code from the reference's logged draws instead of the generator.
 // Everything is integer arithmetic; the only floating-point expressions of the reference's loop (:1682, :2282) are
 // evaluated on the host with the reference's own types when the per-read plan is made.
-#include "reads.h"
+#include "reads_core.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include <chrono>
 
 namespace sp {
-
-constexpr int RD_THREADS = 128;  // reads in flight per CTA
-constexpr unsigned FULL = 0xffffffffu;
-
-// Seed of read `read_index` (0-based) of sequence `ref_num` in per-read-stream mode: splitmix64 finaliser -> [1, 2^31-2].
-__host__ __device__ inline uint32_t read_seed(uint32_t seed, int64_t ref_num, int64_t read_index) {
-    uint64_t z = (uint64_t)seed * 0x9E3779B97F4A7C15ULL + (uint64_t)ref_num * 0xBF58476D1CE4E5B9ULL +
-                 (uint64_t)read_index * 0x94D049BB133111EBULL;
-    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ULL;
-    z ^= z >> 27; z *= 0x94D049BB133111EBULL;
-    z ^= z >> 31;
-    return (uint32_t)(1 + z % 2147483646ULL);
-}
-
-__device__ __forceinline__ uint32_t fastmod(uint32_t a, uint32_t M, uint32_t sh, uint32_t d) {
-    const uint32_t q = (uint32_t)(((uint64_t)a * M) >> sh);
-    return a - q * d;
-}
-__device__ __forceinline__ uint32_t fastmod(uint32_t a, const FastMod* p) {
-    const uint4 v = __ldg((const uint4*)p);
-    return fastmod(a, v.x, v.y, v.z);
-}
-__device__ __forceinline__ FastMod make_fastmod_dev(uint32_t d) {
-    FastMod f;
-    const uint32_t l = d <= 1 ? 0 : 32 - __clz(d - 1);
-    f.sh = 31 + l;
-    f.M = (uint32_t)(((1ull << f.sh) + d - 1) / d);
-    f.d = d; f.pad = 0;
-    return f;
-}
-
-// glibc srand(s), 1 <= s <= 2^31-2 (random_r.c TYPE_3: degree 31, separation 3): r[i] = 16807 * r[i-1] mod (2^31-1), then
-// 310 outputs of r[f] += r[b] (f = 3, b = 0 at the start) are discarded; afterwards f is 3 again.
-__device__ __forceinline__ void glibc_seed(uint32_t s, uint32_t (&r)[31]) {
-    uint64_t w = s;
-    r[0] = s;
-#pragma unroll
-    for (int i = 1; i < 31; i++) { w = (w * 16807ull) % 2147483647ull; r[i] = (uint32_t)w; }
-#pragma unroll 1
-    for (int round = 0; round < 10; round++) {
-#pragma unroll
-        for (int j = 0; j < 31; j++) r[(j + 3) % 31] += r[j];
-    }
-}
 
 // The read's rand(): the thread's own glibc generator (state column in shared memory) or the replayed log.
 template <bool REPLAY>
@@ -114,38 +70,8 @@ struct DrawStream {
     }
 };
 
-struct ReadJob {
-    const uint8_t* seq;  // the sequence reads are drawn from (a haplotype resident in HBM)
-    int64_t L;
-    int64_t n_reads;
-    const int32_t* order; // read indices grouped by (accuracy class, length): 32 consecutive entries share a warp
-    const int32_t* len;   // emitted length per read (:1642-1650, quota clipping applied)
-    const uint8_t* acc;   // accuracy class (:1654-1655)
-    const int32_t* ndel;  // del_num_total (:2282)
-    const int64_t* rec_off;  // n_reads+1 record offsets in `out`
-    uint32_t seed;
-    int64_t ref_num;
-    int32_t no_error;
-    const int32_t* replay;      // nullptr in per-read-stream mode
-    const int64_t* replay_off;
-    uint8_t* out;
-    uint8_t* dropped;
-    uint32_t* used;
-    uint32_t* scratch;          // per warp: [2][scratch_words][32] words — quality codes, then deletion counters
-    int64_t scratch_words;      // words per lane per array (4 positions each)
-    unsigned long long* ctr;    // [0] next read, [1] error code, [2] error read, [3] dropped reads, [4] dropped bytes
-    char id[64];                // ">" + id_prefix + ref_num + "_"
-    int32_t id_len;
-};
-
-__device__ __forceinline__ void job_error(const ReadJob& J, int code, int64_t r) {
-    if (atomicCAS(&J.ctr[1], 0ull, (unsigned long long)code) == 0ull) J.ctr[2] = (unsigned long long)r;
-}
-
 // The oriented, upper-cased template (:2316-2341): seq[t] for t in [0, len'), fetched through aligned 8-byte chunks.
 // The strand is data (a step of +-1 and an xor mask), not a branch: the threads of a warp alternate strands.
-constexpr int LUT_REV_OFFSET = 288;  // bytes between the two strand tables (a shift of 8 banks: 'A' on one strand and
-                                     // 'A' on the other fall into different banks)
 struct Template {
     const unsigned long long* base8;  // 8-byte aligned address at or below seq[0]
     int32_t o0;                       // seq[0] - base8, 0..7
@@ -202,13 +128,6 @@ struct SeqOut {
         out[seq0 + n] = '\n';
     }
 };
-
-__device__ __forceinline__ uint32_t hmm_tran(const ReadTablesDev& T, int a51, uint32_t st, uint32_t d) {
-    return __ldg(T.tran2state + (a51 + st) * 101 + fastmod(d, T.mod_tran + a51 + st) + 1);
-}
-__device__ __forceinline__ uint32_t hmm_emis(const ReadTablesDev& T, int a51, uint32_t st, uint32_t d) {
-    return __ldg(T.emis2qc + (a51 + st) * 101 + fastmod(d, T.mod_emis + a51 + st) + 1);
-}
 
 // One read, start to end, by one thread (simulate_by_model :1657-1711 + mutate :2260-2413).
 template <bool REPLAY>
@@ -426,6 +345,51 @@ reads_kernel(const ReadJob J, const ReadTablesDev T) {
         if (my < J.n_reads) simulate_read<REPLAY>(J, T, s_thre, S, qw, dw, (int64_t)J.order[my], mask);
         __syncwarp();
     }
+}
+
+// The second design of the per-read code (csrc/reads_core.cuh: one draw per step at a ring position the compiler knows,
+// quality codes and deletion counters of four positions in one 8-byte scratch row). Same launch shape and scratch size.
+template <bool REPLAY, bool NOERR, int MIN_CTAS>
+__global__ void __launch_bounds__(RD_THREADS, MIN_CTAS)
+reads_sync_kernel(const ReadJob J, const ReadTablesDev T) {
+    __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
+    __shared__ int32_t s_thre[RD_TABLE_WORDS];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    fill_cta_tables(s_thre, T.thre, threadIdx.x, blockDim.x, 0);
+    __syncthreads();
+    fill_cta_tables(s_thre, T.thre, threadIdx.x, blockDim.x, 1);
+    __syncthreads();
+    CtaTables C;
+    C.bind(s_thre);
+    const int64_t gw = (int64_t)blockIdx.x * (RD_THREADS / 32) + w;
+    uint2* qd = (uint2*)(J.scratch + gw * 2 * J.scratch_words * 32) + lane;
+    Draws<REPLAY> S;
+    S.st = s_state + (REPLAY ? 0 : threadIdx.x);
+    S.replay = nullptr; S.used = 0; S.f = 3;
+    for (;;) {
+        unsigned long long b0 = 0;
+        if (lane == 0) b0 = atomicAdd(&J.ctr[0], 32ull);
+        const int64_t base = (int64_t)__shfl_sync(FULL, b0, 0);
+        if (base >= J.n_reads) break;
+        const int64_t my = base + lane;
+        const unsigned mask = __ballot_sync(FULL, my < J.n_reads);
+        if (my < J.n_reads) simulate_read_sync<REPLAY, NOERR>(J, T, C, S, qd, J.order[my], mask);
+        __syncwarp();
+    }
+}
+
+// Which per-read code runs: 2 = reads_sync_kernel (default), 1 = the first design (reads_kernel). SYNTHPOP_READS_KERNEL and
+// SYNTHPOP_READS_MIN_CTAS (10, 9 or 8 CTAs per SM: 48, 56 or 64 registers per thread) are A/B hooks for bench and profiling
+// runs; every choice produces the same bytes (tests/test_reads_gpu.py runs its cases on both designs).
+using ReadKernel = void (*)(const ReadJob, const ReadTablesDev);
+static ReadKernel pick_read_kernel(bool replay, bool no_error) {
+    int version = 2, min_ctas = 10;
+    if (const char* e = getenv("SYNTHPOP_READS_KERNEL")) version = atoi(e) == 1 ? 1 : 2;
+    if (const char* e = getenv("SYNTHPOP_READS_MIN_CTAS")) min_ctas = atoi(e);
+    if (version == 1) return replay ? reads_kernel<true> : reads_kernel<false>;
+    if (replay) return no_error ? reads_sync_kernel<true, true, 10> : reads_sync_kernel<true, false, 10>;
+    if (no_error) return reads_sync_kernel<false, true, 10>;
+    return min_ctas == 8 ? reads_sync_kernel<false, false, 8> : min_ctas == 9 ? reads_sync_kernel<false, false, 9> : reads_sync_kernel<false, false, 10>;
 }
 
 // First two draws of reads [r0, r0+n) in per-read-stream mode (length and accuracy, :1642, :1654).
@@ -754,10 +718,10 @@ static void launch_batch(sp_ctx* c, ReadState& R, cudaStream_t ks) {
         // chunks and the scratch words live in L1. Measured at 30x chr1: the driver's default split (5 CTAs per SM, large
         // L1) 88 ms, the largest carve-out (8 CTAs per SM) 119 ms. SYNTHPOP_READS_CARVEOUT (percent) is a tuning hook.
         if (const char* e = getenv("SYNTHPOP_READS_CARVEOUT"))   // the attribute is per device: set on every launch (cheap)
-            SP_CUDA(cudaFuncSetAttribute(reads_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
+            SP_CUDA(cudaFuncSetAttribute(pick_read_kernel(replay, p.no_error), cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
     }
-    if (replay) SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<true>, RD_THREADS, 0));
-    else SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, reads_kernel<false>, RD_THREADS, 0));
+    const ReadKernel kernel = pick_read_kernel(replay, p.no_error);
+    SP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kernel, RD_THREADS, 0));
     ctas_per_sm = std::max(1, ctas_per_sm);
     if (const char* e = getenv("SYNTHPOP_READS_CTAS_PER_SM")) ctas_per_sm = std::max(1, std::min(ctas_per_sm, atoi(e)));  // tuning hook
     const int64_t want_ctas = (n_reads + RD_THREADS - 1) / RD_THREADS;
@@ -782,8 +746,7 @@ static void launch_batch(sp_ctx* c, ReadState& R, cudaStream_t ks) {
     J.id_len = (int32_t)id.size();
     if (!R.ev0) { SP_CUDA(cudaEventCreate(&R.ev0)); SP_CUDA(cudaEventCreate(&R.ev1)); }
     SP_CUDA(cudaEventRecord(R.ev0, ks));
-    if (replay) reads_kernel<true><<<grid, RD_THREADS, 0, ks>>>(J, R.dev);
-    else reads_kernel<false><<<grid, RD_THREADS, 0, ks>>>(J, R.dev);
+    kernel<<<grid, RD_THREADS, 0, ks>>>(J, R.dev);
     c->launches++;
     SP_CUDA(cudaGetLastError());
     SP_CUDA(cudaEventRecord(R.ev1, ks));

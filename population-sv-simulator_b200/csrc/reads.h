@@ -108,6 +108,7 @@ struct ReadState {
 };
 
 void reads_configure(sp_ctx* c, const sp_read_args* a);
+void reads_set_params(ReadState& R, const sp_read_args* a);  // host half of reads_configure
 void reads_build_tables(ReadState& R);
 void free_reads(sp_ctx* c);
 // read_mix.cu: the records of R's last batch become the next source of the mix (the buffers change owner)

@@ -124,6 +124,31 @@ def test_per_read_streams_match_the_restatement(sp, oracle_lib, tmp_path, kind, 
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("design,min_ctas", [("1", "10"), ("2", "9"), ("2", "8")])
+def test_every_kernel_variant_writes_the_same_bytes(sp, oracle_lib, tmp_path, monkeypatch, design, min_ctas):
+    """The first design of the per-read code and the register variants of the second (csrc/reads.cu pick_read_kernel) against
+    the restatement, replay and per-read streams; the default (design 2, 10 CTAs per SM) is what every other test runs."""
+    monkeypatch.setenv("SYNTHPOP_READS_KERNEL", design)
+    monkeypatch.setenv("SYNTHPOP_READS_MIN_CTAS", min_ctas)
+    hap = _haplotype(400_000, seed=4)
+    model = _model(tmp_path, "hmm")
+    want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=31, per_read_streams=True, ref_num=2, **CCS)
+    want_r, log_r = oh.pbsim_simulate(oracle_lib, hap, model, seed=32, **CCS)
+    draws = oh.glibc_rand(oracle_lib, 32, log_r["total_draws"])
+    with sp.Context(0, 42) as ctx:
+        _configure(sp, ctx, CCS, 31, model, False, sp.READS_PER_READ_STREAMS)
+        res = ctx.reads_simulate_sequence(hap, ref_num=2)
+        got = ctx.reads_copy(res["file_bytes"])
+        _, dr, used = ctx.reads_log(res["n_reads"])
+        assert np.array_equal(used.astype(np.int64), log["draws_used"]) and np.array_equal(dr, log["dropped"])
+        assert np.array_equal(got, want)
+        _configure(sp, ctx, CCS, 32, model, False, sp.READS_REPLAY)
+        ctx.reads_set_replay(draws, log_r["draw_offset"])
+        res = ctx.reads_simulate_sequence(hap)
+        got = ctx.reads_copy(res["file_bytes"])
+        assert np.array_equal(got, want_r)
+
+
 def test_reads_from_a_materialised_haplotype_never_leave_the_device(sp, oracle_lib, tmp_path):
     """PrintHaplotypes -> pbsim without the .fa file: plan + materialise + read kernel on the resident haplotype."""
     rng = np.random.default_rng(77)
