@@ -68,6 +68,17 @@ struct DrawStream {
         used++;
         return v >> 1;
     }
+    // takes the last n rand() calls back: r[f] += r[f-3] is undone by r[f] -= r[f-3] in reverse order
+    __device__ __forceinline__ void undraw(int n) {
+        used -= (uint32_t)n;
+        if (!REPLAY) {
+            for (int i = 0; i < n; i++) {
+                f = f == 0 ? 30 : f - 1;
+                const int b = f >= 3 ? f - 3 : f + 28;
+                st[f * RD_THREADS] -= st[b * RD_THREADS];
+            }
+        }
+    }
 };
 
 // The oriented, upper-cased template (:2316-2341): seq[t] for t in [0, len'), fetched through aligned 8-byte chunks.
@@ -79,18 +90,57 @@ struct Template {
     const uint8_t* lut;               // shared memory: byte -> upper-cased base (+) or its complement (-), :2316-2341
     int32_t cur;                      // index (relative to base8) of the cached 8-byte chunk
     uint32_t lo, hi;
+    int32_t nw;                       // PF bit 3: index of the chunk held in (nlo, nhi), requested at the last base index
+    uint32_t nlo, nhi;                // that is a multiple of 8 — by every lane in the same step
     __device__ __forceinline__ void begin(const uint8_t* w, int32_t lp, bool forward, const uint8_t* s_lut) {
         const uint8_t* origin = forward ? w : w + (lp - 1);  // first base of the window (+) or its last base (-)
         o0 = (int32_t)((uintptr_t)origin & 7);
         base8 = (const unsigned long long*)(origin - o0);
         dir = forward ? 1 : -1; lut = forward ? s_lut : s_lut + LUT_REV_OFFSET; cur = INT32_MIN; lo = hi = 0;
+        nw = INT32_MIN; nlo = nhi = 0;
     }
+    // PF bit 3: the lanes of a warp cross their chunk boundaries in different steps, so with a load at the crossing some lane
+    // makes the warp wait for memory in EVERY step (a quarter of all stall samples, profiles/r02j). Here every lane requests the
+    // chunk after its current one in the SAME step, once per 8 bases (k is the warp's common base index), into a second
+    // register pair; a crossing is then a register move, and only the crossings right behind the common request still wait.
+    // A lane that jumps over a whole chunk (deletions) or starts a read falls back to the load at the crossing.
+    template <int PF>
+    __device__ __forceinline__ uint8_t at_k(int32_t t, int32_t k, int32_t lp) {
+        const int32_t rel = o0 + dir * t;
+        const int32_t w = rel >> 3;
+        if (w != cur) {
+            if (w == nw) { lo = nlo; hi = nhi; }
+            else {
+                const unsigned long long chunk = __ldg(base8 + w);
+                lo = (uint32_t)chunk; hi = (uint32_t)(chunk >> 32);
+            }
+            cur = w;
+        }
+        if ((k & 7) == 0) {
+            nw = w + dir;
+            if (dir * (nw - ((o0 + dir * (lp - 1)) >> 3)) <= 0) {   // still a chunk of this read's window (which lies inside the sequence)
+                const unsigned long long chunk = __ldg(base8 + nw);
+                nlo = (uint32_t)chunk; nhi = (uint32_t)(chunk >> 32);
+            } else nw = INT32_MIN;
+        }
+        return lut[__byte_perm(lo, hi, (uint32_t)(rel & 7)) & 0xffu];
+    }
+    // PF bit 0: two bases before the lane leaves its chunk, the next chunk is requested into L1 (a prefetch has no
+    // destination register, so no lane's request makes the warp wait); bit 2: on entering a 128-byte line, the next line is
+    // requested into L2.
+    template <int PF>
     __device__ __forceinline__ uint8_t at(int32_t t) {
         const int32_t rel = o0 + dir * t;   // 32-bit: a read is far shorter than 2^31 bases
         const int32_t w = rel >> 3;         // floor, also for the negative offsets of the reverse strand
         if (w != cur) {
             const unsigned long long chunk = __ldg(base8 + w);
             lo = (uint32_t)chunk; hi = (uint32_t)(chunk >> 32); cur = w;
+            if (PF & 4) {
+                if ((w & 15) == (dir > 0 ? 0 : 15)) asm volatile("prefetch.global.L2 [%0];" ::"l"(base8 + (w + 16 * dir)));
+            }
+        }
+        if (PF & 1) {
+            if ((rel & 7) == ((7 + 5 * dir) >> 1)) asm volatile("prefetch.global.L1 [%0];" ::"l"(base8 + (w + dir)));
         }
         return lut[__byte_perm(lo, hi, (uint32_t)(rel & 7)) & 0xffu];
     }
@@ -118,6 +168,24 @@ struct SeqOut {
             prev = cur; cur = 0;
         }
     }
+    // the same with the accumulator as a shift register (two funnel shifts instead of a variable 64-bit shift and two ORs)
+    __device__ __forceinline__ void put_shift(int32_t k, uint8_t c) {
+        cur = (cur >> 8) | ((uint64_t)c << 56);
+        if ((k & 7) == 7) {
+            const int64_t g = (seq0 & ~7ll) + (k - 7);
+            if (k == 7) {
+                for (uint32_t b = a8; b < 64; b += 8) out[g + (b >> 3)] = (uint8_t)(cur >> (b - a8));
+            } else {
+                const uint64_t w = a8 ? (prev >> (64 - a8)) | (cur << a8) : cur;
+                *(uint64_t*)(out + g) = w;
+            }
+            prev = cur; cur = 0;
+        }
+    }
+    __device__ __forceinline__ void finish_shift(int32_t n) {
+        if (n & 7) cur >>= 8 * (8 - (n & 7));   // the pending bases sit in the top bytes of the shift register
+        finish(n);
+    }
     // bases [0, n) were put; writes what is still pending, then the record's closing '\n'
     __device__ __forceinline__ void finish(int32_t n) {
         const int32_t done = n >= 8 ? (n & ~7) - (int32_t)(a8 >> 3) : 0;  // stream bytes already in memory
@@ -130,7 +198,7 @@ struct SeqOut {
 };
 
 // One read, start to end, by one thread (simulate_by_model :1657-1711 + mutate :2260-2413).
-template <bool REPLAY>
+template <bool REPLAY, int PF>
 __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTablesDev& T, const int32_t* s_thre, DrawStream<REPLAY>& S,
                                               uint32_t* qw, uint32_t* dw, int64_t r, unsigned mask) {
     // `mask` = the lanes of this warp that hold a read. Trip counts differ a little between the threads of a warp; the
@@ -202,6 +270,46 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
         const uint32_t qm = min(min(qmin4 & 255u, (qmin4 >> 8) & 255u), min((qmin4 >> 16) & 255u, qmin4 >> 24));
         const int32_t tmax = s_thre[3 * PB_NQ + min(qm, (uint32_t)(PB_NQ - 1))];
         int32_t num = 0;
+        if (PF & 16) {
+            // Two attempts in flight: the scattered read of q[pos] is a trip to HBM for one byte, and the attempt after it
+            // cannot start before it is answered (15 % of all stall samples, profiles/r02k). The draws of the attempts do
+            // not depend on the answers, only their NUMBER does: attempts j+1 and j+2 are drawn (and their reads requested)
+            // before attempt j is decided, and when attempt j turns out to be the last one the four draws made beyond it
+            // are taken back (undraw). Same rand() calls in the same order for everything that counts. Each attempt has its
+            // own registers (the loop is unrolled by three), so no attempt's read is waited for by another attempt's code.
+            uint32_t p0 = 0, p1 = 0, p2 = 0, q0 = 0, q1 = 0, q2 = 0;
+            int32_t v0 = 0, v1 = 0, v2 = 0;
+            bool live = num < ndel;
+#define SP_START(P, V, Q)                                                           \
+    {                                                                               \
+        P = fastmod(S.next(), ml.M, ml.sh, ml.d);                                   \
+        V = (int32_t)(S.next() % 1000000u);                                         \
+        if (V < tmax) Q = qw[(P >> 2) * 32];                                        \
+    }
+#define SP_RESOLVE(P, V, Q)                                                         \
+    {                                                                               \
+        if (V < tmax) {                                                             \
+            const uint32_t sh = 8 * (P & 3);                                        \
+            if (V < s_thre[(Q >> sh) & 255u]) {                                     \
+                asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(dw + (P >> 2) * 32), "r"(1u << sh) : "memory"); \
+                num++;                                                              \
+            }                                                                       \
+        }                                                                           \
+        if (num >= ndel) { S.undraw(4); live = false; }                             \
+    }
+            if (live) { SP_START(p0, v0, q0) SP_START(p1, v1, q1) }
+#pragma unroll 1
+            for (;;) {
+                if (!__any_sync(mask, live)) break;
+                if (live) { SP_START(p2, v2, q2) SP_RESOLVE(p0, v0, q0) }
+                if (!__any_sync(mask, live)) break;
+                if (live) { SP_START(p0, v0, q0) SP_RESOLVE(p1, v1, q1) }
+                if (!__any_sync(mask, live)) break;
+                if (live) { SP_START(p1, v1, q1) SP_RESOLVE(p2, v2, q2) }
+            }
+#undef SP_START
+#undef SP_RESOLVE
+        } else
 #pragma unroll 1
         for (;;) {
             const bool more = num < ndel;
@@ -254,15 +362,33 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
         const bool more = k < len;
         if (!__any_sync(mask, more)) break;
         if (more) {
-            if ((k & 3) == 0) { wq = qw[(k >> 2) * 32]; wd = ndel > 0 ? dw[(k >> 2) * 32] : 0u; }
+            if ((k & 3) == 0) {
+                wq = qw[(k >> 2) * 32]; wd = ndel > 0 ? dw[(k >> 2) * 32] : 0u;
+                if (PF & 2) {   // the rows two loads ahead, into L1 (the scratch has two rows of slack at its end)
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(qw + ((k >> 2) + 2) * 32));
+                    if (ndel > 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(dw + ((k >> 2) + 2) * 32));
+                }
+            }
             const int qv = wq & 255u; wq >>= 8;
             const int32_t dc = wd & 255u; wd >>= 8;
             dsum += dc;
-            const uint8_t nt = Tm.at(t);
+            const uint8_t nt = (PF & 8) ? Tm.at_k<PF>(t, k, lenp) : Tm.at<PF>(t);
             const int32_t d = (int32_t)(S.next() % 1000000u);
             uint8_t outc = nt;
             int32_t adv = 1;
             if (d < s_thre[2 * PB_NQ + qv]) {  // an error event: ins_thre >= sub_thre (:1455-1459), so one test screens both
+                if ((PF & 32) && d < s_thre[PB_NQ + qv]) {   // the same tables as shifts of a constant: no load on this path
+                    const uint32_t sh = 8 * (S.next() % 3u);
+                    if (nt == 'A') outc = (uint8_t)(0x434754u >> sh);        // "TGC"
+                    else if (nt == 'T') outc = (uint8_t)(0x434741u >> sh);   // "AGC"
+                    else if (nt == 'G') outc = (uint8_t)(0x435441u >> sh);   // "ATC"
+                    else if (nt == 'C') outc = (uint8_t)(0x475441u >> sh);   // "ATG"
+                    else outc = (uint8_t)(0x43475441u >> (8 * (S.next() % 4u)));   // "ATGC"
+                } else if (PF & 32) {
+                    const uint32_t idx = S.next() % 8u;
+                    if (idx < 4) outc = (uint8_t)(0x43475441u >> (8 * idx));
+                    adv = 0;
+                } else
                 if (d < s_thre[PB_NQ + qv]) {  // substitution (:2362-2378), per-base tables of set_mut :2211-2214
                     uint32_t idx = S.next() % 3u;
                     if (nt == 'A') outc = "TGC"[idx];
@@ -278,20 +404,26 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
             }
             t += adv + dc;
             if (emit) {
-                nrun = outc == 'N' ? nrun + 1 : 0;
-                drop |= nrun >= 5;
-                O.put(k, outc);
+                if (PF & 32) {
+                    if (outc != 'N') nrun = k + 1;        // here nrun is the index after the last base that is not 'N'
+                    else if (k + 1 - nrun >= 5) drop = true;
+                    O.put_shift(k, outc);
+                } else {
+                    nrun = outc == 'N' ? nrun + 1 : 0;
+                    drop |= nrun >= 5;
+                    O.put(k, outc);
+                }
             }
         }
     }
     __syncwarp(mask);
     if (bad) { J.dropped[r] = 1; J.used[r] = 0; return; }
     if (dsum != ndel) job_error(J, 3, r);
-    if (emit) O.finish(len);
+    if (emit) { if (PF & 32) O.finish_shift(len); else O.finish(len); }
     else {  // pbsim2noError.cpp:1711 prints mut.seq, the oriented template of length len'
 #pragma unroll 1
         for (int32_t i = 0; i < lenp; i++) {
-            const uint8_t c = Tm.at(i);
+            const uint8_t c = Tm.at<0>(i);
             nrun = c == 'N' ? nrun + 1 : 0;
             drop |= nrun >= 5;
             O.put(i, c);
@@ -307,7 +439,7 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
 }
 
 // 10 CTAs per SM (48 registers, a few spilled words): measured best against 8, 9 and 12 with the default carve-out
-template <bool REPLAY>
+template <bool REPLAY, int PF>
 __global__ void __launch_bounds__(RD_THREADS, 10)
 reads_kernel(const ReadJob J, const ReadTablesDev T) {
     __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
@@ -342,7 +474,7 @@ reads_kernel(const ReadJob J, const ReadTablesDev T) {
         if (base >= J.n_reads) break;
         const int64_t my = base + lane;
         const unsigned mask = __ballot_sync(FULL, my < J.n_reads);
-        if (my < J.n_reads) simulate_read<REPLAY>(J, T, s_thre, S, qw, dw, (int64_t)J.order[my], mask);
+        if (my < J.n_reads) simulate_read<REPLAY, PF>(J, T, s_thre, S, qw, dw, (int64_t)J.order[my], mask);
         __syncwarp();
     }
 }
@@ -378,15 +510,23 @@ reads_sync_kernel(const ReadJob J, const ReadTablesDev T) {
     }
 }
 
-// Which per-read code runs: 2 = reads_sync_kernel (default), 1 = the first design (reads_kernel). SYNTHPOP_READS_KERNEL and
-// SYNTHPOP_READS_MIN_CTAS (10, 9 or 8 CTAs per SM: 48, 56 or 64 registers per thread) are A/B hooks for bench and profiling
-// runs; every choice produces the same bytes (tests/test_reads_gpu.py runs its cases on both designs).
+// Which per-read code runs: 1 = the first design (reads_kernel, default, with the variant bits of SYNTHPOP_READS_PF: 2 scratch
+// rows requested two loads ahead, 8 template chunk requested by all lanes in the same step, 16 two deletion attempts in
+// flight, 32 shift-register output and table-free error path), 2 = reads_sync_kernel (csrc/reads_core.cuh).
+// SYNTHPOP_READS_KERNEL, SYNTHPOP_READS_PF and SYNTHPOP_READS_MIN_CTAS are A/B hooks for bench and profiling runs; every
+// choice produces the same bytes (tests/test_reads_gpu.py::test_every_kernel_variant_writes_the_same_bytes).
 using ReadKernel = void (*)(const ReadJob, const ReadTablesDev);
 static ReadKernel pick_read_kernel(bool replay, bool no_error) {
-    int version = 2, min_ctas = 10;
-    if (const char* e = getenv("SYNTHPOP_READS_KERNEL")) version = atoi(e) == 1 ? 1 : 2;
+    int version = 1, min_ctas = 10;
+    if (const char* e = getenv("SYNTHPOP_READS_KERNEL")) version = atoi(e) == 2 ? 2 : 1;
     if (const char* e = getenv("SYNTHPOP_READS_MIN_CTAS")) min_ctas = atoi(e);
-    if (version == 1) return replay ? reads_kernel<true> : reads_kernel<false>;
+    if (version == 1) {
+        int pf = 58;
+        if (const char* e = getenv("SYNTHPOP_READS_PF")) pf = atoi(e);   // variants of the first design (bits: see simulate_read)
+        if (replay) return reads_kernel<true, 0>;
+        return pf == 2 ? reads_kernel<false, 2> : pf == 8 ? reads_kernel<false, 8> : pf == 10 ? reads_kernel<false, 10>
+             : pf == 26 ? reads_kernel<false, 26> : pf == 32 ? reads_kernel<false, 32> : pf == 58 ? reads_kernel<false, 58> : reads_kernel<false, 0>;
+    }
     if (replay) return no_error ? reads_sync_kernel<true, true, 10> : reads_sync_kernel<true, false, 10>;
     if (no_error) return reads_sync_kernel<false, true, 10>;
     return min_ctas == 8 ? reads_sync_kernel<false, false, 8> : min_ctas == 9 ? reads_sync_kernel<false, false, 9> : reads_sync_kernel<false, false, 10>;
@@ -729,7 +869,7 @@ static void launch_batch(sp_ctx* c, ReadState& R, cudaStream_t ks) {
     const int64_t words = ((int64_t)R.cur_max_len + 3) / 4 + 1;
     const size_t cta_scratch = (size_t)(RD_THREADS / 32) * 2 * words * 32 * sizeof(uint32_t);
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(grid_full, (int64_t)((16ull << 30) / cta_scratch)));  // <= 16 GiB of scratch
-    R.d_scratch.reserve(cta_scratch * grid, 0.0);
+    R.d_scratch.reserve(cta_scratch * grid + 4096, 0.0);   // slack: row prefetches run two rows past a lane's last row
     if (!R.h_ctr) SP_CUDA(cudaHostAlloc((void**)&R.h_ctr, 8 * sizeof(unsigned long long), cudaHostAllocDefault));
 
     ReadJob J{};

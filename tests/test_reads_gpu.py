@@ -124,12 +124,13 @@ def test_per_read_streams_match_the_restatement(sp, oracle_lib, tmp_path, kind, 
     assert np.array_equal(got, want)
 
 
-@pytest.mark.parametrize("design,min_ctas", [("1", "10"), ("2", "9"), ("2", "8")])
-def test_every_kernel_variant_writes_the_same_bytes(sp, oracle_lib, tmp_path, monkeypatch, design, min_ctas):
+@pytest.mark.parametrize("design,min_ctas,pf", [("1", "10", "0"), ("1", "10", "2"), ("1", "10", "10"), ("1", "10", "26"), ("1", "10", "32"), ("1", "10", "58"), ("2", "10", "0"), ("2", "9", "0"), ("2", "8", "0")])
+def test_every_kernel_variant_writes_the_same_bytes(sp, oracle_lib, tmp_path, monkeypatch, design, min_ctas, pf):
     """The first design of the per-read code and the register variants of the second (csrc/reads.cu pick_read_kernel) against
     the restatement, replay and per-read streams; the default (design 2, 10 CTAs per SM) is what every other test runs."""
     monkeypatch.setenv("SYNTHPOP_READS_KERNEL", design)
     monkeypatch.setenv("SYNTHPOP_READS_MIN_CTAS", min_ctas)
+    monkeypatch.setenv("SYNTHPOP_READS_PF", pf)
     hap = _haplotype(400_000, seed=4)
     model = _model(tmp_path, "hmm")
     want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=31, per_read_streams=True, ref_num=2, **CCS)

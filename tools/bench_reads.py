@@ -21,13 +21,14 @@ with sp.Context(0, 42) as ctx:
             "--depth", str(depth), "--hmm_model", model, "--seed", "42"]
     args, _ = sp.ReadArgs.from_options(opts, stream_mode=sp.READS_PER_READ_STREAMS)
     ctx.reads_configure(args)
-    # PROFILE_VARIANTS: comma list of <design>:<min CTAs per SM> (csrc/reads.cu pick_read_kernel), A/B in one process
+    # PROFILE_VARIANTS: comma list of <design>:<min CTAs per SM>[:<prefetch bits>] (csrc/reads.cu pick_read_kernel), A/B in one process
     for variant in os.environ.get("PROFILE_VARIANTS", "2:10").split(","):
-        design, min_ctas = variant.split(":")
+        design, min_ctas, pf = (variant.split(":") + ["0"])[:3]
         os.environ["SYNTHPOP_READS_KERNEL"] = design
         os.environ["SYNTHPOP_READS_MIN_CTAS"] = min_ctas
+        os.environ["SYNTHPOP_READS_PF"] = pf
         for it in range(int(os.environ.get("PROFILE_ITERS", 3))):
             r = ctx.reads_simulate_sequence(bases)
             t = ctx.reads_timing()
-            print(f"design {design} min_ctas {min_ctas}: reads {r['n_reads']} bases {r['bases']} kernel {t['kernel_ms']:.2f} ms "
+            print(f"design {design} min_ctas {min_ctas} pf {pf}: reads {r['n_reads']} bases {r['bases']} kernel {t['kernel_ms']:.2f} ms "
                   f"plan {t['plan_ms']:.2f} ms -> {r['bases'] / t['kernel_ms'] / 1e6:.1f} Gbp/s", flush=True)
