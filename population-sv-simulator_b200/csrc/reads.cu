@@ -484,7 +484,7 @@ reads_kernel(const ReadJob J, const ReadTablesDev T) {
 template <bool REPLAY, bool NOERR, int MIN_CTAS>
 __global__ void __launch_bounds__(RD_THREADS, MIN_CTAS)
 reads_sync_kernel(const ReadJob J, const ReadTablesDev T) {
-    __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
+    __shared__ uint32_t s_state[REPLAY ? 32 : RING * RD_THREADS];
     __shared__ int32_t s_thre[RD_TABLE_WORDS];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     fill_cta_tables(s_thre, T.thre, threadIdx.x, blockDim.x, 0);
@@ -497,7 +497,7 @@ reads_sync_kernel(const ReadJob J, const ReadTablesDev T) {
     uint2* qd = (uint2*)(J.scratch + gw * 2 * J.scratch_words * 32) + lane;
     Draws<REPLAY> S;
     S.st = s_state + (REPLAY ? 0 : threadIdx.x);
-    S.replay = nullptr; S.used = 0; S.f = 3;
+    S.replay = nullptr; S.used = 0; S.pos = 31;
     for (;;) {
         unsigned long long b0 = 0;
         if (lane == 0) b0 = atomicAdd(&J.ctr[0], 32ull);
@@ -524,8 +524,7 @@ static ReadKernel pick_read_kernel(bool replay, bool no_error) {
         int pf = 58;
         if (const char* e = getenv("SYNTHPOP_READS_PF")) pf = atoi(e);   // variants of the first design (bits: see simulate_read)
         if (replay) return reads_kernel<true, 0>;
-        return pf == 2 ? reads_kernel<false, 2> : pf == 8 ? reads_kernel<false, 8> : pf == 10 ? reads_kernel<false, 10>
-             : pf == 26 ? reads_kernel<false, 26> : pf == 32 ? reads_kernel<false, 32> : pf == 58 ? reads_kernel<false, 58> : reads_kernel<false, 0>;
+        return pf == 0 ? reads_kernel<false, 0> : pf == 10 ? reads_kernel<false, 10> : pf == 26 ? reads_kernel<false, 26> : reads_kernel<false, 58>;
     }
     if (replay) return no_error ? reads_sync_kernel<true, true, 10> : reads_sync_kernel<true, false, 10>;
     if (no_error) return reads_sync_kernel<false, true, 10>;

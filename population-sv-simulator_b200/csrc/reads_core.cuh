@@ -3,20 +3,26 @@
 // very same functions one lane at a time on the CPU and compares them with the restatement — a logic check that needs no
 // GPU; it is test infrastructure, the library never runs this code on the host).
 //
-// Second design of the per-read code ("one draw per step"): the glibc generator r[i] = r[i-31] + r[i-3] lives in a
-// shared-memory column per thread, and what made the first design expensive was the RING POSITION of a draw being a
-// run-time value in two of the three phases (12 instructions per draw, 5 with a position the compiler knows). Here the
-// ring is physically rotated to position 0 before the deletion loop and again before the pass over the bases (31 loads +
-// 31 stores, twice per read), and both loops are unrolled over 31 ring positions:
-//   * deletion loop: an attempt is two draws, 31 attempts are two laps of the ring;
-//   * pass over the bases: every lane of a warp makes exactly ONE draw per step, at the same ring position. What the draw
-//     means is the lane's own business: the error decision of its next base (the common case), or — after an error event —
-//     the substitution / insertion index the reference draws next (:2362-2387). A lane therefore falls behind the step
-//     counter by one base per extra draw, keeps its own base index, and loads its quality word / stores its output word
-//     under its own predicate. Nothing is ever drawn out of order: lane by lane the sequence of rand() calls is the
-//     reference's.
+// Second design of the per-read code ("one draw per step"). The glibc generator r[i] = r[i-31] + r[i-3] lives in a
+// shared-memory column per thread; in the first design (csrc/reads.cu) the ring position of a draw is a run-time value of
+// each thread in two of the three phases (12 instructions per draw), and the pass over the bases costs 129 warp
+// instructions per base because 55 % of the steps have some lane in the error path (two more draws with run-time
+// positions). Here:
+//   * the ring has 32 slots (value i lives in slot i & 31; it reads slots i+1 = i-31 and i-3 and writes slot i), so positions
+//     wrap by masking and a block of four consecutive draws that starts at a multiple of four needs no wrap inside;
+//   * the ring is physically rotated to slot 0 before the deletion loop and again before the pass over the bases (32 moves,
+//     twice per read), after which every lane of a warp is at the SAME slot: the slot is loop state of the warp, not of the
+//     thread, and inside a block of four draws every address is a base register plus a constant;
+//   * in the pass over the bases every lane makes exactly ONE draw per step. What the draw means is the lane's own business:
+//     the error decision of its next base (the common case), or — after an error event — the substitution / insertion
+//     index the reference draws next (:2362-2387). A lane falls behind the step counter by one base per extra draw, keeps
+//     its own base index, and loads its quality row / stores its output word under its own predicate. Lane by lane the
+//     sequence of rand() calls is the reference's.
 // Output words are aligned to the RECORD's position in the file (the accumulator is a shift register, a full aligned
 // 8-byte word is stored as it is), so there is no funnel shift per word and no second accumulator.
+// (A first version unrolled both loops over all 31 positions of a 31-slot ring: 41 % fewer instructions in the deletion
+// loop, but 94 ms against 75 ms — 60 KB of straight-line code, sm__icc_request_hit_rate fell and stall_no_instruction rose
+// from 0.24 to 3.6 warps per issue, profiles/r02j.)
 #pragma once
 #include "reads.h"
 
@@ -93,6 +99,13 @@ SP_HD void red_add_u32(uint32_t* p, uint32_t v) {  // fire-and-forget: nothing w
     asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 #else
     *p += v;
+#endif
+}
+SP_HD void prefetch_l1(const void* p) {  // a request with no destination register: no lane's request makes the warp wait
+#ifdef __CUDA_ARCH__
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+    (void)p;
 #endif
 }
 SP_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {  // low word of (hi:lo) >> sh, 0 <= sh < 32
@@ -219,62 +232,86 @@ SP_HD void fill_cta_tables(int32_t* s_thre, const int32_t* thre, int tid, int nt
     }
 }
 
-// The read's rand(): the thread's own glibc generator (state column: word j of this thread is st[j * RD_THREADS]) or the
-// replayed log.
+// The read's rand(): the thread's own glibc generator (state column: slot j of this thread is st[j * RD_THREADS], 32
+// slots) or the replayed log. `pos` = the slot the next value goes to.
+constexpr int RING = 32;
 template <bool REPLAY>
 struct Draws {
     uint32_t* st;
     const int32_t* replay;  // first logged draw of this read
     uint32_t used;          // rand() calls so far
-    int f;                  // glibc's front index (rear = f - 3 mod 31)
+    int pos;
     SP_HD void seed(uint32_t s) {
         uint32_t r[31];
-        glibc_seed(s, r);
+        glibc_seed(s, r);   // glibc's front index is 3 afterwards: its next output is r[3] += r[0], so r[(3 + j) % 31] is value j of 31
 #pragma unroll
-        for (int j = 0; j < 31; j++) st[j * RD_THREADS] = r[j];
-        f = 3; used = 0;
+        for (int j = 0; j < 31; j++) st[j * RD_THREADS] = r[(3 + j) % 31];
+        pos = 31; used = 0;
     }
-    // rand() at a ring position the caller knows at compile time: no index arithmetic; f and used are brought up to date by
-    // the caller once the unrolled block is over
-    SP_HD uint32_t next_at(int fi) {
+    // rand() at a slot the caller knows at compile time; pos and used are brought up to date by the caller
+    SP_HD uint32_t next_at(int slot) {
         if (REPLAY) return (uint32_t)ld_ro(replay + used++);
-        const int b = fi >= 3 ? fi - 3 : fi + 28;
-        const uint32_t v = st[fi * RD_THREADS] + st[b * RD_THREADS];
-        st[fi * RD_THREADS] = v;
+        const uint32_t v = st[((slot + 1) & 31) * RD_THREADS] + st[((slot + 29) & 31) * RD_THREADS];
+        st[slot * RD_THREADS] = v;
         return v >> 1;
     }
     SP_HD void skip(uint32_t n) {  // account for n draws made through next_at
         if (REPLAY) return;
         used += n;
-        f = (int)((uint32_t)(f + n) % 31u);
+        pos = (int)((uint32_t)(pos + n) & 31u);
     }
     SP_HD uint32_t next() {
         if (REPLAY) return (uint32_t)ld_ro(replay + used++);
-        const int b = f >= 3 ? f - 3 : f + 28;
-        const uint32_t v = st[f * RD_THREADS] + st[b * RD_THREADS];
-        st[f * RD_THREADS] = v;
-        f = f == 30 ? 0 : f + 1;
+        const uint32_t v = st[((pos + 1) & 31) * RD_THREADS] + st[((pos + 29) & 31) * RD_THREADS];
+        st[pos * RD_THREADS] = v;
+        pos = (pos + 1) & 31;
         used++;
         return v >> 1;
     }
-    // Physical rotation of the ring: word (j + f) mod 31 moves to word j, afterwards the front index is 0. 31 is prime, so
-    // for f != 0 the moves form one cycle 0 <- f <- 2f <- ... ; one temporary.
+    // Physical rotation of the ring: slot (j + pos) & 31 moves to slot j, afterwards pos is 0. The moves form gcd(32, pos)
+    // cycles; one flat loop of 32 moves walks them one after the other (c = the cycle's first slot, t0 = its old value).
     SP_HD void rotate() {
         if (REPLAY) return;
-        const int s = f;
+        const int s = pos;
         if (s != 0) {
-            const uint32_t t0 = st[0];
-            int j = 0;
+            int c = 0, j = 0;
+            uint32_t t0 = st[0];
 #pragma unroll 1
-            for (int i = 0; i < 30; i++) {
-                int nj = j + s;
-                nj = nj >= 31 ? nj - 31 : nj;
-                st[j * RD_THREADS] = st[nj * RD_THREADS];
-                j = nj;
+            for (int i = 0; i < 32; i++) {
+                const int nj = (j + s) & 31;
+                if (nj == c) {
+                    st[j * RD_THREADS] = t0;
+                    c++; j = c;
+                    t0 = st[(c & 31) * RD_THREADS];
+                } else {
+                    st[j * RD_THREADS] = st[nj * RD_THREADS];
+                    j = nj;
+                }
             }
-            st[j * RD_THREADS] = t0;
         }
-        f = 0;
+        pos = 0;
+    }
+};
+
+// Four consecutive draws at slots p..p+3, p a multiple of four known to the whole warp: every address is one of three base
+// pointers (the blocks before, at and after p) plus a constant.
+template <bool REPLAY>
+struct DrawBlock {
+    uint32_t *prev, *cur, *next;
+    SP_HD void begin(Draws<REPLAY>& S) {   // S.pos == 0
+        prev = S.st + 28 * RD_THREADS; cur = S.st; next = S.st + 4 * RD_THREADS;
+    }
+    SP_HD void advance(Draws<REPLAY>& S, int p_after_next) {   // p_after_next = (p + 8) & 31 of the block that ends
+        prev = cur; cur = next; next = S.st + p_after_next * RD_THREADS;
+    }
+    template <int J>
+    SP_HD uint32_t draw(Draws<REPLAY>& S) {   // draw J (0..3) of the block
+        if (REPLAY) return (uint32_t)ld_ro(S.replay + S.used++);
+        const uint32_t ahead = J < 3 ? cur[(J + 1) * RD_THREADS] : next[0];
+        const uint32_t back = J >= 3 ? cur[(J - 3) * RD_THREADS] : prev[(J + 1) * RD_THREADS];
+        const uint32_t v = ahead + back;
+        cur[J * RD_THREADS] = v;
+        return v >> 1;
     }
 };
 
@@ -316,21 +353,38 @@ struct TemplateWindow {
     uint32_t strand_off;              // 0 / LUT_REV_OFFSET
     int32_t cur;                      // index (relative to base8) of the cached 8-byte chunk
     uint32_t lo, hi;
+    int32_t nw;                       // index of the chunk in (nlo, nhi): request_next
+    uint32_t nlo, nhi;
     SP_HD void begin(const uint8_t* w, int32_t lp, bool forward) {
         const uint8_t* origin = forward ? w : w + (lp - 1);  // first base of the window (+) or its last base (-)
         o0 = (int32_t)((uintptr_t)origin & 7);
         base8 = (const unsigned long long*)(origin - o0);
         dir = (int32_t)keep_in_register(forward ? 1u : 0xffffffffu);
         strand_off = forward ? 0u : (uint32_t)LUT_REV_OFFSET; cur = INT32_MIN; lo = hi = 0;
+        nw = INT32_MIN; nlo = nhi = 0;
     }
     SP_HD uint32_t at(int32_t t, const CtaTables& C) {
         const int32_t rel = o0 + dir * t;   // 32-bit: a read is far shorter than 2^31 bases
         const int32_t w = rel >> 3;         // floor, also for the negative offsets of the reverse strand
         if (w != cur) {
-            const unsigned long long chunk = ld_ro(base8 + w);
-            lo = (uint32_t)chunk; hi = (uint32_t)(chunk >> 32); cur = w;
+            if (w == nw) { lo = nlo; hi = nhi; }   // the chunk every lane requested in the same step (request_next)
+            else {
+                const unsigned long long chunk = ld_ro(base8 + w);
+                lo = (uint32_t)chunk; hi = (uint32_t)(chunk >> 32);
+            }
+            cur = w;
         }
         return C.base_of(strand_off, byte_perm(lo, hi, (uint32_t)(rel & 7)) & 0xffu);
+    }
+    // The lanes of a warp cross their chunk boundaries in different steps: with a load at the crossing, some lane makes the
+    // warp wait for memory in every step. Called by every lane in the same step, once per 8 steps: the chunk after the
+    // current one goes into a second register pair, and a crossing is a register move. lp = the window's length.
+    SP_HD void request_next(int32_t lp) {
+        const int32_t w = cur + dir;
+        if (cur != INT32_MIN && dir * (w - ((o0 + dir * (lp - 1)) >> 3)) <= 0) {   // still a chunk of this read's window
+            const unsigned long long chunk = ld_ro(base8 + w);
+            nlo = (uint32_t)chunk; nhi = (uint32_t)(chunk >> 32); nw = w;
+        }
     }
 };
 
@@ -381,30 +435,77 @@ SP_HD uint32_t hmm_emis(const ReadTablesDev& T, int a51, uint32_t st, uint32_t d
     return ld_ro(T.emis2qc + (a51 + st) * 101 + fastmod(d, T.mod_emis + a51 + st) + 1);
 }
 
-// The draw AFTER an error decision (:2362-2387). `pend` = mode | nt << 8 | dc << 16. mode 1: substitution index for the
-// template base nt (per-base tables of set_mut :2211-2214); a base that is none of ACGT draws again (mode 2: one of
-// "ATGC"). mode 3: insertion, the template base is not consumed. Returns outc | adv << 8 | finished << 9. A pure function
-// of two scalars, kept out of line: it runs for 0.3 % of the draws and would otherwise be copied into each of the 31
-// unrolled steps.
-SP_HD_NOINLINE uint32_t error_draw(uint32_t pend, uint32_t d) {
+// The draw AFTER an error decision (:2362-2387), as arithmetic on constants (the reference's per-base tables of set_mut
+// :2211-2214 are three characters each). `pend` = mode | nt << 8 | dc << 16. mode 1: substitution index for the template base
+// nt; a base that is none of ACGT draws again (mode 2: one of "ATGC"). mode 3: insertion, the template base is not
+// consumed. Returns outc | adv << 8 | finished << 9.
+SP_HD uint32_t error_draw(uint32_t pend, uint32_t d) {
     const uint32_t mode = pend & 255u, nt = (pend >> 8) & 255u;
-    uint32_t outc = nt, adv = 1, fin = 1;
     if (mode == 1) {
-        const uint32_t sh = 8 * (d % 3u);
-        if (nt == 'A') outc = (0x434754u >> sh) & 255u;        // "TGC"
-        else if (nt == 'T') outc = (0x434741u >> sh) & 255u;   // "AGC"
-        else if (nt == 'G') outc = (0x435441u >> sh) & 255u;   // "ATC"
-        else if (nt == 'C') outc = (0x475441u >> sh) & 255u;   // "ATG"
-        else fin = 0;
-    } else if (mode == 2) {
-        outc = (0x43475441u >> (8 * (d % 4u))) & 255u;         // "ATGC"
-    } else {
-        const uint32_t idx = d % 8u;
-        if (idx < 4) outc = (0x43475441u >> (8 * idx)) & 255u;
-        adv = 0;
+        const uint32_t tab = nt == 'A' ? 0x434754u      // "TGC"
+                           : nt == 'T' ? 0x434741u      // "AGC"
+                           : nt == 'G' ? 0x435441u      // "ATC"
+                           : nt == 'C' ? 0x475441u      // "ATG"
+                           : 0u;
+        return tab ? (((tab >> (8 * (d % 3u))) & 255u) | 0x300u) : (nt | 0x100u);
     }
-    return outc | adv << 8 | fin << 9;
+    if (mode == 2) return ((0x43475441u >> (8 * (d & 3u))) & 255u) | 0x300u;   // "ATGC"
+    return ((d & 4u) ? nt : ((0x43475441u >> (8 * (d & 3u))) & 255u)) | 0x200u;   // insertion: idx = d % 8, idx < 4 draws a base
 }
+
+// The pass over the bases (:2348-2401) as the state of one lane; step<J>() is one draw of a block of four.
+template <bool REPLAY, bool NOERR>
+struct BaseLoop {
+    int32_t k, len;     // this lane's next base, the read's length
+    int32_t t;          // template index: advances with every base except after an insertion, and over deleted bases
+    uint32_t pend;      // 0: the step's draw decides base k; else an error event of base k waits for its draw (error_draw)
+    uint32_t wq, wd;    // what is left of the current scratch row: quality codes, deletion counters
+    uint32_t nq, nd;    // the next row, requested by every lane that had used up its last one at the start of a block of four
+    bool have;          // steps (a lane enters at most one new row per block), so that entering a row is a register move
+    uint32_t nrare, nins;   // draws that went to error_draw, insertions
+    const uint2* row;   // the lane's next scratch row
+    TemplateWindow Tm;
+    RecordWords O;
+
+    SP_HD void request_row() {
+        if (!have) {
+            const uint2 w = *row;   // at most one row past the read's last: inside the lane's scratch
+            nq = w.x; nd = w.y;
+            row += 32;
+            have = true;
+        }
+    }
+    template <int J>
+    SP_HD void step(Draws<REPLAY>& S, DrawBlock<REPLAY>& B, const CtaTables& C) {
+        if (k < len) {
+            const uint32_t d = B.template draw<J>(S);
+            uint32_t outc, adv, dc;
+            bool fin;
+            if (pend == 0) {
+                if ((k & 3) == 0) { wq = nq; wd = nd; have = false; }
+                const uint32_t qv = wq & 255u;
+                dc = wd & 255u;
+                wq >>= 8; wd >>= 8;
+                outc = Tm.at(t, C);
+                adv = 1;
+                const int32_t dm = (int32_t)(d % 1000000u);
+                fin = dm >= C.ins_thre(qv);   // ins_thre >= sub_thre (:1455-1459): one test screens both kinds of event
+                if (!fin) pend = (dm < C.sub_thre(qv) ? 1u : 3u) | outc << 8 | dc << 16;
+            } else {
+                const uint32_t e = error_draw(pend, d);
+                nrare++;
+                outc = e & 255u; adv = (e >> 8) & 1u; fin = (e & 0x200u) != 0; dc = pend >> 16;
+                nins += fin ? (adv ^ 1u) : 0u;
+                pend = fin ? 0u : ((pend & ~255u) | 2u);   // a template base that is none of ACGT: one more draw
+            }
+            if (fin) {
+                t += (int32_t)(adv + dc);
+                if (!NOERR) O.put(outc);
+                k++;
+            }
+        }
+    }
+};
 
 // One read, start to end, by one thread. qd = this lane's scratch: row i holds {4 quality codes, 4 deletion counters} of
 // positions 4i..4i+3 as one uint2, rows interleaved by lane (qd[i * 32]), so the sequential passes are coalesced 8-byte
@@ -422,26 +523,27 @@ SP_HD void simulate_read_sync(const ReadJob& J, const ReadTablesDev& T, const Ct
     }
     if (REPLAY) { S.replay = J.replay + J.replay_off[r]; S.used = 0; }
     else S.seed(read_seed(J.seed, J.ref_num, r));
-    S.next(); S.next();  // the length and accuracy draws (:1642, :1654), evaluated when the plan was made
+    S.next(); S.next();  // the length and accuracy draws (:1642, :1654), evaluated when the plan was made: the next slot is 1
     warp_sync(mask);
 
     // ---- quality codes (:1657-1680), four per scratch row; the deletion counters are cleared on the way. Every read
-    // reaches this point after the same number of draws: blocks of 31 bases are unrolled with compile-time ring positions.
+    // reaches this point after the same number of draws, so the slot of each quality draw is a function of the base index
+    // alone: blocks of 16 (two draws per base) or 32 bases are unrolled with compile-time slots.
     uint32_t qmin4 = 0xffffffffu;  // bytewise minimum of the quality words: bounds every acceptance threshold below
     if (T.exist_hmm[acc]) {
         const int a51 = acc * 51;
-        uint32_t st = ld_ro(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);  // third draw: f is 6 now
+        uint32_t st = ld_ro(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);  // third draw, slot 1
         uint32_t word = 0;
-        if (len > 0) word = hmm_emis(T, a51, st, S.next_at(6));
-        // base p >= 1 draws at ring positions 5+2p (transition) and 6+2p (emission), mod 31
+        if (len > 0) word = hmm_emis(T, a51, st, S.next_at(2));
+        // base p >= 1 draws at slots 1+2p (transition) and 2+2p (emission), mod 32
 #pragma unroll 1
-        for (int32_t p0 = 1; p0 < len; p0 += 31) {
+        for (int32_t p0 = 1; p0 < len; p0 += 16) {
 #pragma unroll
-            for (int j = 0; j < 31; j++) {
+            for (int j = 0; j < 16; j++) {
                 const int32_t p = p0 + j;
                 if (p < len) {
-                    st = hmm_tran(T, a51, st, S.next_at((7 + 2 * j) % 31));
-                    word |= hmm_emis(T, a51, st, S.next_at((8 + 2 * j) % 31)) << (8 * (p & 3));
+                    st = hmm_tran(T, a51, st, S.next_at((3 + 2 * j) & 31));
+                    word |= hmm_emis(T, a51, st, S.next_at((4 + 2 * j) & 31)) << (8 * (p & 3));
                     if ((p & 3) == 3) { qd[(p >> 2) * 32] = make_uint2(word, 0u); qmin4 = vminu4(qmin4, word); word = 0; }
                 }
             }
@@ -452,14 +554,14 @@ SP_HD void simulate_read_sync(const ReadJob& J, const ReadTablesDev& T, const Ct
         const uint4 mf = ld_ro4(T.mod_freq + acc);
         const uint8_t* f2q = T.freq2qc + acc * 1001;
         uint32_t word = 0;
-        // two draws so far (f is 5): base p draws at ring position 5+p mod 31
+        // two draws so far: base p draws at slot 1+p mod 32
 #pragma unroll 1
-        for (int32_t p0 = 0; p0 < len; p0 += 31) {
+        for (int32_t p0 = 0; p0 < len; p0 += 32) {
 #pragma unroll
-            for (int j = 0; j < 31; j++) {
+            for (int j = 0; j < 32; j++) {
                 const int32_t p = p0 + j;
                 if (p < len) {
-                    word |= (uint32_t)ld_ro(f2q + fastmod(S.next_at((5 + j) % 31), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
+                    word |= (uint32_t)ld_ro(f2q + fastmod(S.next_at((1 + j) & 31), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
                     if ((p & 3) == 3) { qd[(p >> 2) * 32] = make_uint2(word, 0u); qmin4 = vminu4(qmin4, word); word = 0; }
                 }
             }
@@ -470,7 +572,7 @@ SP_HD void simulate_read_sync(const ReadJob& J, const ReadTablesDev& T, const Ct
     S.rotate();
     warp_sync(mask);
 
-    // ---- deletions by rejection (:2282-2292): an attempt is two draws, 31 attempts are two laps of the ring
+    // ---- deletions by rejection (:2282-2292): an attempt is two draws, a block of four draws is two attempts
     {
         const FastMod ml = make_fastmod_dev((uint32_t)(len - 1 > 1 ? len - 1 : 1));
         const uint32_t q0 = qmin4 & 255u, q1 = (qmin4 >> 8) & 255u, q2 = (qmin4 >> 16) & 255u, q3 = qmin4 >> 24;
@@ -480,40 +582,45 @@ SP_HD void simulate_read_sync(const ReadJob& J, const ReadTablesDev& T, const Ct
         const int32_t tmax = C.err_thre_max_from(qm < (uint32_t)(PB_NQ - 1) ? qm : (uint32_t)(PB_NQ - 1));
         int32_t num = 0;
         uint32_t att = 0;
+        int p = 0;   // the block's first slot: the same for every lane of the warp
+        DrawBlock<REPLAY> B;
+        B.begin(S);
+#define SP_ATTEMPT(J0, J1)                                                                                              \
+    if (num < ndel) {                                                                                                   \
+        const uint32_t pos = fastmod(B.template draw<J0>(S), ml.M, ml.sh, ml.d);                                        \
+        const int32_t v = (int32_t)(B.template draw<J1>(S) % 1000000u);                                                 \
+        att++;                                                                                                          \
+        /* v >= the largest threshold any position of this read can have: rejected whatever q[pos] is, and the */      \
+        /* scattered read of q[pos] (one HBM access for one byte) is not made. Same decision, same draws. */            \
+        if (v < tmax) {                                                                                                 \
+            const uint32_t sh = 8 * (pos & 3);                                                                          \
+            uint32_t* rw = (uint32_t*)(qd + (pos >> 2) * 32);                                                           \
+            const uint32_t qv = (rw[0] >> sh) & 255u;                                                                   \
+            if (v < C.err_thre(qv)) {                                                                                   \
+                /* one more deletion after position pos: a reduction, no load to wait for. A counter byte that wraps */ \
+                /* (more than 255 deletions at one position) shows up as a wrong total below. */                        \
+                red_add_u32(rw + 1, 1u << sh);                                                                          \
+                num++;                                                                                                  \
+            }                                                                                                           \
+        }                                                                                                               \
+    }
 #pragma unroll 1
         for (;;) {
             if (!warp_any(mask, num < ndel)) break;
-#pragma unroll
-            for (int j = 0; j < 31; j++) {
-                if (num < ndel) {
-                    const uint32_t pos = fastmod(S.next_at((2 * j) % 31), ml.M, ml.sh, ml.d);
-                    const int32_t v = (int32_t)(S.next_at((2 * j + 1) % 31) % 1000000u);
-                    att++;
-                    // v >= the largest threshold any position of this read can have: rejected whatever q[pos] is, and the
-                    // scattered read of q[pos] (one HBM access for one byte) is not made. Same decision, same draws.
-                    if (v < tmax) {
-                        const uint32_t sh = 8 * (pos & 3);
-                        uint32_t* row = (uint32_t*)(qd + (pos >> 2) * 32);
-                        const uint32_t qv = (row[0] >> sh) & 255u;
-                        if (v < C.err_thre(qv)) {
-                            // one more deletion after position pos: a reduction, no load to wait for. A counter byte that
-                            // wraps (more than 255 deletions at one position) shows up as a wrong total below.
-                            red_add_u32(row + 1, 1u << sh);
-                            num++;
-                        }
-                    }
-                }
-            }
+            SP_ATTEMPT(0, 1)
+            SP_ATTEMPT(2, 3)
+            B.advance(S, (p + 8) & 31);
+            p = (p + 4) & 31;
         }
-        if (!REPLAY) { S.used += 2u * att; S.f = (int)((2u * att) % 31u); }
+#undef SP_ATTEMPT
+        if (!REPLAY) { S.used += 2u * att; S.pos = (int)((2u * att) & 31u); }
     }
 
     // ---- start offset (:2306-2311), header
     const uint32_t offset = bad ? 0u : S.next() % (uint32_t)(J.L - (len + ndel) + 1);
     S.rotate();
-    TemplateWindow Tm;
-    Tm.begin(J.seq + offset, len + ndel, (r & 1) == 0);  // res_num % 2 == 0 before the increment (:2316)
-    RecordWords O;
+    BaseLoop<REPLAY, NOERR> W;
+    W.Tm.begin(J.seq + offset, len + ndel, (r & 1) == 0);  // res_num % 2 == 0 before the increment (:2316)
     {
         int64_t o = J.rec_off[r];
         if (!bad) {  // ">S<ref>_<n>Z", a dozen bytes
@@ -524,69 +631,46 @@ SP_HD void simulate_read_sync(const ReadJob& J, const ReadTablesDev& T, const Ct
             while (nd > 0) J.out[o++] = (uint8_t)dig[--nd];
             J.out[o++] = 'Z';
         }
-        O.begin(J.out, o);
+        W.O.begin(J.out, o);
     }
 
-    // ---- the bases (:2348-2401), one draw per step for every lane
-    int32_t k = 0;      // this lane's next base
-    int32_t t = 0;      // template index: advances with every base except after an insertion, and over deleted bases
-    uint32_t pend = 0;  // 0: the step's draw decides base k; else an error event of base k waits for its draw (error_draw)
-    uint32_t wq = 0, wd = 0;
-    uint32_t nrare = 0, nins = 0;  // draws that went to error_draw, insertions
-    warp_sync(mask);
+    // ---- the bases (:2348-2401), one draw per step for every lane, four steps per block
+    W.k = 0; W.len = len; W.t = 0; W.pend = 0; W.wq = 0; W.wd = 0; W.nrare = 0; W.nins = 0; W.row = qd;
+    W.nq = 0; W.nd = 0; W.have = false;
+    {
+        int p = 0;
+        DrawBlock<REPLAY> B;
+        B.begin(S);
+        warp_sync(mask);
 #pragma unroll 1
-    for (;;) {
-        if (!warp_any(mask, k < len)) break;
-#pragma unroll
-        for (int s = 0; s < 31; s++) {
-            if (k < len) {
-                const uint32_t d = S.next_at(s);
-                if (pend == 0) {
-                    if ((k & 3) == 0) { const uint2 w = qd[(k >> 2) * 32]; wq = w.x; wd = w.y; }
-                    const uint32_t qv = wq & 255u, dc = wd & 255u;
-                    wq >>= 8; wd >>= 8;
-                    const uint32_t nt = Tm.at(t, C);
-                    const int32_t dm = (int32_t)(d % 1000000u);
-                    if (dm < C.ins_thre(qv)) {  // an error event: ins_thre >= sub_thre (:1455-1459), one test screens both
-                        pend = (dm < C.sub_thre(qv) ? 1u : 3u) | nt << 8 | dc << 16;
-                    } else {
-                        t += (int32_t)(1u + dc);
-                        if (!NOERR) O.put(nt);
-                        k++;
-                    }
-                } else {
-                    const uint32_t e = error_draw(pend, d);
-                    nrare++;
-                    if (e & 0x200u) {
-                        const uint32_t adv = (e >> 8) & 1u;
-                        nins += adv ^ 1u;
-                        t += (int32_t)(adv + (pend >> 16));
-                        if (!NOERR) O.put(e & 255u);
-                        k++;
-                        pend = 0;
-                    } else {
-                        pend = (pend & ~255u) | 2u;   // a template base that is none of ACGT: one more draw
-                    }
-                }
-            }
+        for (;;) {
+            if (!warp_any(mask, W.k < len)) break;
+            W.request_row();
+            if ((p & 4) == 0) W.Tm.request_next(len + ndel);
+            W.template step<0>(S, B, C);
+            W.template step<1>(S, B, C);
+            W.template step<2>(S, B, C);
+            W.template step<3>(S, B, C);
+            B.advance(S, (p + 8) & 31);
+            p = (p + 4) & 31;
         }
     }
     warp_sync(mask);
     if (bad) { J.dropped[r] = 1; J.used[r] = 0; return; }
     len = J.len[r]; ndel = J.ndel[r];
-    if (!REPLAY) S.used += (uint32_t)len + nrare;
+    if (!REPLAY) S.used += (uint32_t)len + W.nrare;
     // every deletion was met along the read: t = (bases that consumed a template base) + (deletions); a counter byte that
     // wrapped loses 256 here
-    if (t != len - (int32_t)nins + ndel) job_error(J, 3, r);
-    if (!NOERR) O.finish();
+    if (W.t != len - (int32_t)W.nins + ndel) job_error(J, 3, r);
+    if (!NOERR) W.O.finish();
     else {  // pbsim2noError.cpp:1711 prints mut.seq, the oriented template of length len'
 #pragma unroll 1
-        for (int32_t i = 0; i < len + ndel; i++) O.put(Tm.at(i, C));
-        O.finish();
+        for (int32_t i = 0; i < len + ndel; i++) W.O.put(W.Tm.at(i, C));
+        W.O.finish();
     }
-    J.dropped[r] = O.drop ? 1 : 0;
+    J.dropped[r] = W.O.drop ? 1 : 0;
     J.used[r] = S.used;
-    if (O.drop) job_count_dropped(J, (unsigned long long)(J.rec_off[r + 1] - J.rec_off[r]));
+    if (W.O.drop) job_count_dropped(J, (unsigned long long)(J.rec_off[r + 1] - J.rec_off[r]));
 }
 
 }  // namespace sp

@@ -14,13 +14,13 @@ namespace {
 
 template <bool REPLAY, bool NOERR>
 void run_reads(const ReadJob& J, const ReadTablesDev& T, const int32_t* tables, int64_t words) {
-    std::vector<uint32_t> state((size_t)31 * RD_THREADS, 0u);
+    std::vector<uint32_t> state((size_t)RING * RD_THREADS, 0u);
     std::vector<uint2> scratch((size_t)words * 32);
     CtaTables C;
     C.bind(tables);
     Draws<REPLAY> S;
     S.st = state.data() + 5;   // any column
-    S.replay = nullptr; S.used = 0; S.f = 3;
+    S.replay = nullptr; S.used = 0; S.pos = 31;
     for (int64_t r = 0; r < J.n_reads; r++) {
         for (auto& w : scratch) w = make_uint2(0xdeadbeefu, 0xdeadbeefu);   // nothing may rely on a clean scratch
         simulate_read_sync<REPLAY, NOERR>(J, T, C, S, scratch.data() + 7, (int32_t)r, 1u);
