@@ -150,9 +150,9 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
                "coverage_prefix_bytes_last_individual": sweep}
     achieved = READ_ALGO_BYTES_PER_BASE * bases / (k_ms / 1e3) / 1e9
     # the bound that applies: warp instructions issued per second against 4 per clock per SM, with the
-    # instructions per base of the committed ncu capture (profiles/r02a_reads_kernel_base_raw.csv: 42.76 G for 7.469 G bases)
+    # instructions per base of the committed ncu capture of the default kernel (profiles/r02m_reads_final_raw.csv: 46.86 G for 7.469 G bases)
     props = torch.cuda.get_device_properties(torch.cuda.current_device())
-    ipb = 42758455726 / 7468692660
+    ipb = 46856658240 / 7468692660
     peak_issue = props.multi_processor_count * 4 * 1.965e9
     rate = ipb * bases / (k_ms / 1e3)
     issue = {"bound": "issue", "achieved": rate / 1e12, "peak": peak_issue / 1e12, "unit": "T warp-inst/s",
@@ -167,7 +167,7 @@ def reads_leg(ctx, splib, synth, work, first_hap, n_haps, depth, peak, torch, qu
             "kernel_ms_what": "per individual, the span of its two read kernels in flight together (sp_reads_mix_add_pair)",
             "one_by_one_kernel_ms_warmup_individual": one_by_one_ms,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": 22.3 * bases, "traffic_source": "22.3 B per base, ncu of one launch (profiles/r02a_reads_kernel_base_raw.csv)",
+                         "traffic": 20.9 * bases, "traffic_source": "20.9 B per base (126.9 GB read + 29.5 GB written for 7.469 Gbases), ncu of one launch of the default kernel (profiles/r02m_reads_final_raw.csv)",
                          "kernel": "reads_kernel", "algorithmic_bytes_per_base": READ_ALGO_BYTES_PER_BASE},
             "issue_roofline": issue, "mix": mix_obj}
 
