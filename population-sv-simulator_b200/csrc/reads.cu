@@ -523,7 +523,7 @@ static ReadKernel pick_read_kernel(bool replay, bool no_error) {
     if (version == 1) {
         int pf = 58;
         if (const char* e = getenv("SYNTHPOP_READS_PF")) pf = atoi(e);   // variants of the first design (bits: see simulate_read)
-        if (replay) return reads_kernel<true, 0>;
+        if (replay) return pf == 0 ? reads_kernel<true, 0> : reads_kernel<true, 58>;   // replay runs the default variant's code: the golden vectors of the reference binary pin it
         return pf == 0 ? reads_kernel<false, 0> : pf == 10 ? reads_kernel<false, 10> : pf == 26 ? reads_kernel<false, 26> : reads_kernel<false, 58>;
     }
     if (replay) return no_error ? reads_sync_kernel<true, true, 10> : reads_sync_kernel<true, false, 10>;
