@@ -7,15 +7,19 @@
 // ONE THREAD PER READ (first version: one warp per read around a shared-memory draw ring — 16 warp instructions per
 // base, most of them cooperation overhead; see profiles/r01_reads_kernel_v1_lines.txt .. r01c_reads_kernel_lines.txt):
 //   * the thread runs the reference's loops as they are, with the glibc TYPE_3 generator r[i] = r[i-31] + r[i-3] as
-//     a 31-word circular buffer in shared memory laid out [word][thread] (bank = thread: conflict-free whatever
-//     each thread's phase), one add per draw;
+//     a 32-slot ring in shared memory (csrc/reads_core.cuh: value i in slot i & 31 reads slots i+1 and i-3; positions
+//     wrap by masking) laid out [slot][thread] (bank = thread: conflict-free whatever each thread's phase), one add per
+//     draw;
 //   * a warp takes 32 reads that the host has grouped by (accuracy class, length), so its threads run the same
 //     phases for nearly the same trip counts;
 //   * per-read scratch (quality codes and deletion counters, one byte per position) lives in HBM interleaved
 //     [word][lane], so the sequential passes are 128-byte coalesced and only the rejection loop's lookups scatter;
 //   * the haplotype window is read in aligned 8-byte chunks and the read is written in aligned 8-byte chunks.
-//   * the quality loops are unrolled by 31 bases: every read enters them after the same number of draws, so the ring
-//     position of each quality draw is a compile-time constant there;
+//   * the quality loops are unrolled by one lap of the ring (16 bases at two draws each, or 32): every read enters them
+//     after the same number of draws, so the slot of each quality draw is a compile-time constant there (on a 31-slot
+//     ring the lap was 31 bases and 22 KB of code; the instruction cache served 88 % of the requests);
+//   * the pass over the bases asks for its scratch rows two loads ahead and for the next template chunk in one common
+//     step per 8 bases, the deletion loop keeps two attempts in flight;
 //   * the deletion rejection loop skips the scattered lookup of q[pos] whenever the draw is already above the largest
 //     threshold any position of the read can have (same decisions, same draws);
 //   * in per-read-stream mode the loop header (length, accuracy, quota cut, record offsets, work order) is computed on
@@ -30,56 +34,6 @@
 #include <chrono>
 
 namespace sp {
-
-// The read's rand(): the thread's own glibc generator (state column in shared memory) or the replayed log.
-template <bool REPLAY>
-struct DrawStream {
-    uint32_t* st;           // &state[0][thread]; word j of this thread is st[j * RD_THREADS]
-    const int32_t* replay;  // first logged draw of this read
-    uint32_t used;          // rand() calls so far
-    int f;                  // glibc's front index (rear = f - 3 mod 31)
-    __device__ __forceinline__ void seed(uint32_t s) {
-        uint32_t r[31];
-        glibc_seed(s, r);
-#pragma unroll
-        for (int j = 0; j < 31; j++) st[j * RD_THREADS] = r[j];
-        f = 3; used = 0;
-    }
-    // rand() at a ring position the caller knows at compile time (after unrolling): no index arithmetic, f and used are
-    // brought up to date by skip() once the unrolled block is over
-    __device__ __forceinline__ uint32_t next_at(int fi) {
-        if (REPLAY) return (uint32_t)__ldg(replay + used++);
-        const int b = fi >= 3 ? fi - 3 : fi + 28;
-        const uint32_t v = st[fi * RD_THREADS] + st[b * RD_THREADS];
-        st[fi * RD_THREADS] = v;
-        return v >> 1;
-    }
-    __device__ __forceinline__ void skip(uint32_t n) {  // account for n draws made through next_at
-        if (REPLAY) return;
-        used += n;
-        f = (int)((uint32_t)(f + n) % 31u);
-    }
-    __device__ __forceinline__ uint32_t next() {
-        if (REPLAY) return (uint32_t)__ldg(replay + used++);
-        const int b = f >= 3 ? f - 3 : f + 28;
-        const uint32_t v = st[f * RD_THREADS] + st[b * RD_THREADS];
-        st[f * RD_THREADS] = v;
-        f = f == 30 ? 0 : f + 1;
-        used++;
-        return v >> 1;
-    }
-    // takes the last n rand() calls back: r[f] += r[f-3] is undone by r[f] -= r[f-3] in reverse order
-    __device__ __forceinline__ void undraw(int n) {
-        used -= (uint32_t)n;
-        if (!REPLAY) {
-            for (int i = 0; i < n; i++) {
-                f = f == 0 ? 30 : f - 1;
-                const int b = f >= 3 ? f - 3 : f + 28;
-                st[f * RD_THREADS] -= st[b * RD_THREADS];
-            }
-        }
-    }
-};
 
 // The oriented, upper-cased template (:2316-2341): seq[t] for t in [0, len'), fetched through aligned 8-byte chunks.
 // The strand is data (a step of +-1 and an xor mask), not a branch: the threads of a warp alternate strands.
@@ -199,7 +153,7 @@ struct SeqOut {
 
 // One read, start to end, by one thread (simulate_by_model :1657-1711 + mutate :2260-2413).
 template <bool REPLAY, int PF>
-__device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTablesDev& T, const int32_t* s_thre, DrawStream<REPLAY>& S,
+__device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTablesDev& T, const int32_t* s_thre, Draws<REPLAY>& S,
                                               uint32_t* qw, uint32_t* dw, int64_t r, unsigned mask) {
     // `mask` = the lanes of this warp that hold a read. Trip counts differ a little between the threads of a warp; the
     // __syncwarp(mask) after every phase makes them start the next one together (independent thread scheduling would
@@ -221,22 +175,22 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
     // ---- quality codes (:1657-1680), four per scratch word; the deletion counters are cleared on the way
     uint32_t qmin4 = 0xffffffffu;  // bytewise minimum of the quality words: the read's lowest quality code bounds every
                                    // acceptance threshold of the deletion loop below
-    // Every read reaches this point after the same number of draws, so the ring position of each quality draw is a
-    // function of the base index alone: blocks of 31 bases are unrolled with compile-time ring positions.
+    // Every read reaches this point after the same number of draws, so the slot of each quality draw is a function of
+    // the base index alone: one lap of the ring is unrolled with compile-time slots.
     if (T.exist_hmm[acc]) {
         const int a51 = acc * 51;
-        uint32_t st = __ldg(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);  // third draw: f is 6 now
+        uint32_t st = __ldg(T.init2state + acc * 101 + fastmod(S.next(), T.mod_init + acc) + 1);  // third draw, slot 1
         uint32_t word = 0;
-        if (len > 0) word = hmm_emis(T, a51, st, S.next_at(6));
-        // base p >= 1 draws at ring positions 5+2p (transition) and 6+2p (emission), mod 31
+        if (len > 0) word = hmm_emis(T, a51, st, S.next_at(2));
+        // base p >= 1 draws at slots 1+2p (transition) and 2+2p (emission) of the 32-slot ring: 16 bases per lap
 #pragma unroll 1
-        for (int32_t p0 = 1; p0 < len; p0 += 31) {
+        for (int32_t p0 = 1; p0 < len; p0 += 16) {
 #pragma unroll
-            for (int j = 0; j < 31; j++) {
+            for (int j = 0; j < 16; j++) {
                 const int32_t p = p0 + j;
                 if (p < len) {
-                    st = hmm_tran(T, a51, st, S.next_at((7 + 2 * j) % 31));
-                    word |= hmm_emis(T, a51, st, S.next_at((8 + 2 * j) % 31)) << (8 * (p & 3));
+                    st = hmm_tran(T, a51, st, S.next_at((3 + 2 * j) & 31));
+                    word |= hmm_emis(T, a51, st, S.next_at((4 + 2 * j) & 31)) << (8 * (p & 3));
                     if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; qmin4 = __vminu4(qmin4, word); word = 0; }
                 }
             }
@@ -247,14 +201,14 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
         const uint4 mf = __ldg((const uint4*)(T.mod_freq + acc));
         const uint8_t* f2q = T.freq2qc + acc * 1001;
         uint32_t word = 0;
-        // two draws so far (f is 5): base p draws at ring position 5+p mod 31
+        // two draws so far: base p draws at slot 1+p mod 32
 #pragma unroll 1
-        for (int32_t p0 = 0; p0 < len; p0 += 31) {
+        for (int32_t p0 = 0; p0 < len; p0 += 32) {
 #pragma unroll
-            for (int j = 0; j < 31; j++) {
+            for (int j = 0; j < 32; j++) {
                 const int32_t p = p0 + j;
                 if (p < len) {
-                    word |= (uint32_t)__ldg(f2q + fastmod(S.next_at((5 + j) % 31), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
+                    word |= (uint32_t)__ldg(f2q + fastmod(S.next_at((1 + j) & 31), mf.x, mf.y, mf.z) + 1) << (8 * (p & 3));
                     if ((p & 3) == 3) { qw[(p >> 2) * 32] = word; dw[(p >> 2) * 32] = 0; qmin4 = __vminu4(qmin4, word); word = 0; }
                 }
             }
@@ -442,7 +396,7 @@ __device__ __forceinline__ void simulate_read(const ReadJob& J, const ReadTables
 template <bool REPLAY, int PF>
 __global__ void __launch_bounds__(RD_THREADS, 10)
 reads_kernel(const ReadJob J, const ReadTablesDev T) {
-    __shared__ uint32_t s_state[REPLAY ? 32 : 31 * RD_THREADS];
+    __shared__ uint32_t s_state[REPLAY ? 32 : RING * RD_THREADS];
     __shared__ int32_t s_thre[4 * PB_NQ + (LUT_REV_OFFSET + 256) / 4];  // err_thre, sub_thre, ins_thre, max(err_thre[q..93]), strand tables
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 3 * PB_NQ; i += blockDim.x) s_thre[i] = T.thre[i];
@@ -464,9 +418,9 @@ reads_kernel(const ReadJob J, const ReadTablesDev T) {
     const int64_t gw = (int64_t)blockIdx.x * (RD_THREADS / 32) + w;
     uint32_t* qw = J.scratch + gw * 2 * J.scratch_words * 32 + lane;
     uint32_t* dw = qw + J.scratch_words * 32;
-    DrawStream<REPLAY> S;
+    Draws<REPLAY> S;
     S.st = s_state + (REPLAY ? 0 : threadIdx.x);
-    S.replay = nullptr; S.used = 0; S.f = 3;
+    S.replay = nullptr; S.used = 0; S.pos = 31;
     for (;;) {
         unsigned long long b0 = 0;
         if (lane == 0) b0 = atomicAdd(&J.ctr[0], 32ull);

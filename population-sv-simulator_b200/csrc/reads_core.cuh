@@ -268,6 +268,18 @@ struct Draws {
         used++;
         return v >> 1;
     }
+    // Takes the last n (< 28) rand() calls back. Values i .. i+n-1 went to slots s .. s+n-1 and overwrote values i-32 ..
+    // i-33+n, of which all but the first are read again (value m reads value m-31): value i-32+k = value i+k-1 - value
+    // i+k-4, restored from the highest k down so that every operand is still in place.
+    SP_HD void undraw(int n) {
+        used -= (uint32_t)n;
+        if (!REPLAY) {
+            const int s = (pos - n) & 31;
+            for (int k = n - 1; k >= 1; k--)
+                st[((s + k) & 31) * RD_THREADS] = st[((s + k - 1) & 31) * RD_THREADS] - st[((s + k - 4) & 31) * RD_THREADS];
+            pos = s;
+        }
+    }
     // Physical rotation of the ring: slot (j + pos) & 31 moves to slot j, afterwards pos is 0. The moves form gcd(32, pos)
     // cycles; one flat loop of 32 moves walks them one after the other (c = the cycle's first slot, t0 = its old value).
     SP_HD void rotate() {
