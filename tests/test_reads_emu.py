@@ -69,6 +69,8 @@ def test_replay_through_the_kernel_code_on_the_host(emu, oracle_lib, tmp_path, k
 @pytest.mark.parametrize("kind,no_error,seed,params", [
     ("empty", False, 11, CCS), ("hmm", False, 12, CCS), ("hmm", True, 13, CCS), ("hmm_sparse", False, 14, CCS),
     ("hmm", False, 15, CLR), ("empty", False, 16, dict(CCS, len_min=2, len_mean=40.0, len_sd=30.0, len_max=200, depth=0.5)),
+    ("hmm", False, 77, dict(CCS, len_min=8, len_max=30000, len_mean=2500.0, len_sd=3000.0, depth=3.0)),
+    ("hmm", True, 78, dict(CCS, len_min=8, len_max=30000, len_mean=2500.0, len_sd=3000.0, depth=3.0)),
 ])
 def test_per_read_streams_through_the_kernel_code_on_the_host(emu, oracle_lib, tmp_path, kind, no_error, seed, params):
     """The generator in its shared-memory-column form: compile-time ring positions, two rotations per read."""

@@ -151,6 +151,28 @@ def test_every_kernel_variant_writes_the_same_bytes(sp, oracle_lib, tmp_path, mo
         assert np.array_equal(got, want_r)
 
 
+@pytest.mark.parametrize("design", ["1", "2"])
+@pytest.mark.parametrize("no_error", [False, True])
+def test_short_and_ragged_reads(sp, oracle_lib, tmp_path, monkeypatch, design, no_error):
+    """Lengths from 8 to 30 000 in one run (reads that end inside their first output word, reads shorter than a template
+    chunk or a scratch row, warps whose lanes finish thousands of bases apart), on a sequence short enough that windows
+    touch both of its ends: the requests made ahead of need (next template chunk, scratch rows) stay inside what they may read."""
+    monkeypatch.setenv("SYNTHPOP_READS_KERNEL", design)
+    p = dict(CCS, len_min=8, len_max=30000, len_mean=2500.0, len_sd=3000.0, depth=6.0)
+    hap = _haplotype(120_000, seed=2)
+    model = _model(tmp_path, "hmm")
+    want, log = oh.pbsim_simulate(oracle_lib, hap, model, seed=77, no_error=no_error, per_read_streams=True, ref_num=1, **p)
+    assert log["length"].min() < 64 and log["length"].max() > 8000
+    with sp.Context(0, 42) as ctx:
+        _configure(sp, ctx, p, 77, model, no_error, sp.READS_PER_READ_STREAMS)
+        res = ctx.reads_simulate_sequence(hap)
+        got = ctx.reads_copy(res["file_bytes"])
+        ln, dr, used = ctx.reads_log(res["n_reads"])
+    assert np.array_equal(ln, log["length"]) and np.array_equal(dr, log["dropped"])
+    assert np.array_equal(used.astype(np.int64), log["draws_used"])
+    assert np.array_equal(got, want)
+
+
 def test_reads_from_a_materialised_haplotype_never_leave_the_device(sp, oracle_lib, tmp_path):
     """PrintHaplotypes -> pbsim without the .fa file: plan + materialise + read kernel on the resident haplotype."""
     rng = np.random.default_rng(77)
