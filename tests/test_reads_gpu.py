@@ -247,6 +247,32 @@ def test_pbsim_argument_errors(sp, tmp_path):
             ctx.reads_simulate_sequence(np.frombuffer(b"ACGT" * 10, np.uint8))
 
 
+@pytest.mark.parametrize("design", ["1", "2"])
+def test_reads_the_reference_cannot_simulate_are_refused(sp, tmp_path, monkeypatch, design):
+    """A read of length 1 makes the reference compute rand() % 0 (docker/pbsim2.cpp:2284); a read at least as long as its
+    sequence makes it emit fewer bases than it accounted for. Both kernels stop with an error that names the read; the context
+    stays usable."""
+    monkeypatch.setenv("SYNTHPOP_READS_KERNEL", design)
+    mf = str(tmp_path / "m"); open(mf, "w").close()
+    hap = _haplotype(20_000, seed=1)
+    with sp.Context(0, 42) as ctx:
+        args, _ = sp.ReadArgs.from_options(["--hmm_model", mf, "--depth", "1", "--length-min", "1", "--length-max", "40", "--length-mean", "2",
+                                            "--length-sd", "2", "--seed", "3"])
+        ctx.reads_configure(args)
+        with pytest.raises(sp.SynthpopError, match="length 1"):
+            ctx.reads_simulate_sequence(hap)
+        args, _ = sp.ReadArgs.from_options(["--hmm_model", mf, "--depth", "3", "--length-min", "15000", "--length-max", "90000", "--length-mean",
+                                            "30000", "--length-sd", "9000", "--seed", "3"])
+        ctx.reads_configure(args)
+        with pytest.raises(sp.SynthpopError, match="as long as the sequence"):
+            ctx.reads_simulate_sequence(hap)
+        args, _ = sp.ReadArgs.from_options(["--hmm_model", mf, "--depth", "2", "--length-min", "100", "--length-max", "4000", "--length-mean",
+                                            "1500", "--length-sd", "500", "--seed", "3"])
+        ctx.reads_configure(args)
+        res = ctx.reads_simulate_sequence(hap)
+        assert res["n_reads"] > 10 and res["bases"] >= 2 * hap.size
+
+
 def test_full_size_30x_chr1_properties(sp, tmp_path):
     """BASELINE configs[3] at full size (30x CCS over one chr1-sized haplotype, ~7.5 Gbp of reads): too large for the
     CPU restatement, so the size-independent properties of simulate_by_model are checked instead — the quota rule
